@@ -1,0 +1,85 @@
+/* vc_b200.h — C ABI of libvc_b200.so: hand-written sm_100a (B200) kernels for VerseCrafter's denoise step.
+ *
+ * Conventions: raw device pointers, explicit sizes and strides (in ELEMENTS unless noted), the
+ * caller's cudaStream_t passed as void*; every function only enqueues work on that stream — no allocation, no
+ * synchronisation, no C++ exceptions.  Return value: 0 = OK, < 0 = invalid argument / unsupported (message in
+ * vc_last_error()), > 0 = CUDA error code (cudaError_t, or 1000 + CUresult from tensor-map encoding).
+ * All tensors are bf16 (uint16 storage) unless noted.  The reference has no native code; each entry point replaces
+ * the PyTorch/library calls at the cited lines of /root/reference/versecrafter/models/.
+ */
+#ifndef VC_B200_H
+#define VC_B200_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* library / device probes */
+int vc_version(void);            /* 100 = 0.1.0 */
+int vc_build_arch(void);         /* 100: compiled for sm_100a only */
+int vc_device_ok(void);          /* 0 if the current CUDA device is compute capability 10.x */
+const char* vc_last_error(void); /* thread-local message of the last non-zero return */
+
+/* K3/K4 — LayerNorm (fp32 statistics, eps inside rsqrt, no learned affine) fused with the AdaLN modulation.
+ * mode 0: out[r,:] = LN(x[r,:]) * (1 + scale[b,:]) + shift[b,:],  b = r / rows_per_batch,
+ *         shift/scale rows are mod_batch_stride elements apart  (WanLayerNorm + modulate,
+ *         wan_transformer3d.py:326-346 with :591-592, :603-604; Head :641-643)
+ * mode 1: out[r,:] = LN(x[r,:]) * gamma + beta   (norm3 affine, wan_transformer3d.py:548-550 used at :600);
+ *         pass beta as shift_or_beta and gamma as scale_or_gamma.
+ * D % 8 == 0, D <= 8192; ldx/ldo = row strides. */
+int vc_ln_modulate(const void* x, long long ldx, void* out, long long ldo, const void* shift_or_beta,
+                   const void* scale_or_gamma, long long mod_batch_stride, long long rows, long long rows_per_batch,
+                   int D, float eps, int mode, void* stream);
+
+/* K5 — in place on rows [q(D) | k(D) | ...] (row stride ld): the first n_mats (1 or 2) D-wide column blocks
+ * <- RoPE(RMSNorm_D(.) * gain)  (block 0 uses gain_q, block 1 gain_k; the rest of the row, e.g. v, is untouched).
+ * RMSNorm is over the FULL hidden dim D (WanRMSNorm, wan_transformer3d.py:307-323, applied before the head split
+ * :385-386); RoPE is the 3-axis adjacent-pair rotation of rope_apply (:143-172) with per-axis (cos,sin) tables
+ * rope_table = float2 [grid_f*nf | grid_h*nh | grid_w*nw] (fp32, built from fp64 angles), nf+nh+nw = head_dim/2.
+ * Token position = pos_offset + (row % rows_per_batch)  (pos_offset = first token of this rank under sequence
+ * parallelism); positions >= grid_f*grid_h*grid_w are normalised but not rotated.  apply_rope = 0: RMSNorm only
+ * (cross-attention: q rows with n_mats = 1, :420; text-context [k | v] rows with n_mats = 1, :421). */
+int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset, int D,
+                       int n_mats, const void* gain_q, const void* gain_k, const void* rope_table, int grid_f,
+                       int grid_h, int grid_w, int nf, int nh, int nw, float eps, int apply_rope, void* stream);
+
+/* K8/K9/K10 (+K1/K2 after vc_patchify) — C[M,N] = epilogue(A[M,K] . W[N,K]^T), fp32 accumulation on tcgen05.
+ * W is an nn.Linear weight as stored ([out, in], row-major).  epilogue is a bit mask applied in this order, with a
+ * bf16 rounding wherever the reference's op-by-op bf16 arithmetic has one:
+ *   VC_EPI_BIAS  (1): + bias[N]                         (every nn.Linear on the path, wan_transformer3d.py:366-369)
+ *   VC_EPI_GELU  (2): GELU-tanh                         (ffn.1, :558)
+ *   VC_EPI_GATE  (4): * gate[b, N], b = row / rows_per_batch, gate rows gate_batch_stride apart  (:595, :607)
+ *   VC_EPI_SCALE (16): * scale                          (hint * context_scale, wan_transformer3d_versecrafter.py:147)
+ *   VC_EPI_RES   (8): + residual[M,N] (row stride ldr; may alias C)   (:595, :600, :607; before_proj + x :114)
+ * Supported masks: 0, 1, 3, 9, 13, 25.  N % 8 == 0, K % 8 == 0, lda/ldw/ldc/ldr % 8 == 0, 16-byte aligned bases. */
+#define VC_EPI_BIAS 1
+#define VC_EPI_GELU 2
+#define VC_EPI_GATE 4
+#define VC_EPI_RES 8
+#define VC_EPI_SCALE 16
+int vc_gemm_bf16(const void* A, long long lda, const void* W, long long ldw, void* C, long long ldc, long long M,
+                 long long N, long long K, int epilogue, const void* bias, const void* gate,
+                 long long gate_batch_stride, long long rows_per_batch, const void* residual, long long ldr,
+                 float scale, void* stream);
+
+/* K6/K7 — o = softmax(q k^T * softmax_scale) v, non-causal, all Lk keys attended (no mask other than the tail of
+ * the last 128-key tile).  Replaces videox_fun attention() at wan_transformer3d.py:394-399 (self) and :425-430
+ * (cross).  head_dim must be 128 and contiguous; *_strides = {batch, token, head} strides in elements (so q/k/v
+ * may be column slices of one fused QKV buffer).  variant 0: P staged through shared memory (SS MMA);
+ * variant 1: P kept in tensor memory (TS MMA). */
+int vc_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, int B, int H, int Lq, int Lk,
+                      int head_dim, const long long* q_strides, const long long* k_strides,
+                      const long long* v_strides, const long long* o_strides, float softmax_scale, int variant,
+                      void* stream);
+
+/* K1/K2 front end — one sample [C, F, H, W] -> patch matrix A[L, 4C] (row stride ld_out), K ordered (c, ph, pw),
+ * token n = (f*H/2 + h)*W/2 + w; Conv3d(kernel = stride = (1,2,2)) == vc_gemm_bf16(A, weight.view(D, 4C)) + bias
+ * (wan_transformer3d.py:758-759, wan_transformer3d_versecrafter.py:199-201, :262-263, :340-343). */
+int vc_patchify(const void* in, void* out, int C, int F, int H, int W, long long ld_out, void* stream);
+
+/* a16 back end — y [L, 4*Co] (row stride ldy) -> out [Co, F, 2*gh, 2*gw]  (unpatchify, wan_transformer3d.py:1127-1150) */
+int vc_unpatchify(const void* y, long long ldy, void* out, int Co, int gf, int gh, int gw, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VC_B200_H */

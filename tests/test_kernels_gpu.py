@@ -1,0 +1,205 @@
+"""GPU parity of each sm_100a kernel, called through the C ABI (ctypes), against the oracle's functions
+(oracle/restate.py) on the same seeded inputs.  Tolerances: bf16 outputs, so "equal up to one bf16 rounding":
+relative L2 <= 4e-3 for the row kernels and GEMM epilogues (measured ~1e-3 when a rounding tie flips), <= 1e-2
+for attention (P is rounded to bf16 before the PV product, as in flash-attn)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import restate  # noqa: E402
+
+
+def relerr(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from versecrafter_b200 import _lib, ops
+    lib = _lib.load()
+    assert lib.vc_device_ok() == 0, lib.vc_last_error()
+    return ops
+
+
+def _rand(shape, seed, scale=1.0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(shape, generator=g, device="cuda") * scale).to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("D", [128, 256, 512, 1536, 2048, 5120])
+@pytest.mark.parametrize("rows_per_batch", [1, 77, 333])
+def test_ln_modulate(ops, D, rows_per_batch):
+    B = 2
+    x = _rand((B, rows_per_batch, D), 1, 2.0) + 0.5
+    m = _rand((B, 6, D), 2, 0.3)
+    out = ops.ln_modulate(x, m[:, 0], m[:, 1], rows_per_batch)
+    ref = restate.layer_norm(x) * (1 + m[:, 1:2]) + m[:, 0:1]
+    assert out.shape == x.shape
+    assert relerr(out, ref) < 4e-3
+    assert (out.float() - ref.float()).abs().max() <= 0.07 * ref.float().abs().max()
+
+
+@pytest.mark.parametrize("D", [128, 1536, 5120])
+def test_ln_affine(ops, D):
+    x = _rand((3, 50, D), 3, 1.5)
+    gamma = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    beta = (0.02 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    out = ops.ln_affine(x, gamma, beta)
+    ref = restate.layer_norm(x, gamma, beta)
+    assert relerr(out, ref) < 4e-3
+
+
+@pytest.mark.parametrize("D,H", [(128, 1), (256, 2), (1536, 12), (5120, 40)])
+@pytest.mark.parametrize("grid,pos_offset,rows_per_batch", [((3, 4, 6), 0, 72), ((3, 4, 6), 36, 36), ((2, 3, 5), 0, 37)])
+def test_rmsnorm_rope(ops, D, H, grid, pos_offset, rows_per_batch):
+    """q,k normalised over the full D then rotated per head; v untouched; pad rows (pos >= F*H*W) not rotated;
+    pos_offset emulates a sequence-parallel rank that owns the second half of the tokens."""
+    B = 2
+    d = D // H
+    qkv = _rand((B * rows_per_batch, 3 * D), 4)
+    gq = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    gk = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    ref_in = qkv.clone()
+    rope = ops.rope_table(d, grid, "cuda")
+    ops.rmsnorm_rope_(qkv, D, 2, gq, gk, rows_per_batch, rope=rope, grid=grid, pos_offset=pos_offset)
+    ang = restate.rope_angles(d, grid, device="cuda")
+    L = grid[0] * grid[1] * grid[2]
+    for i, g in enumerate((gq, gk)):
+        u = restate.rms_norm(ref_in[:, i * D:(i + 1) * D], g).view(B, rows_per_batch, H, d)
+        # oracle rotates rows [0, n) of a sequence that starts at position 0: build the full sequence, then slice
+        full = torch.zeros(B, max(L, pos_offset + rows_per_batch), H, d, dtype=u.dtype, device="cuda")
+        full[:, pos_offset:pos_offset + rows_per_batch] = u
+        want = restate.rope_rotate(full, ang)[:, pos_offset:pos_offset + rows_per_batch]
+        got = qkv[:, i * D:(i + 1) * D].view(B, rows_per_batch, H, d)
+        assert relerr(got, want) < 4e-3, i
+    assert torch.equal(qkv[:, 2 * D:], ref_in[:, 2 * D:])
+
+
+def test_rmsnorm_only(ops):
+    D = 1536
+    buf = _rand((100, 2 * D), 5)
+    g = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    ref = restate.rms_norm(buf[:, :D].clone(), g)
+    keep = buf[:, D:].clone()
+    ops.rmsnorm_rope_(buf, D, 1, g, None, 100)
+    assert relerr(buf[:, :D], ref) < 4e-3
+    assert torch.equal(buf[:, D:], keep)
+
+
+def _gemm_ref(a, w, bias, epi, gate=None, rpb=1, res=None, scale=1.0):
+    bf = lambda t: t.to(torch.bfloat16).float()
+    v = a.float() @ w.float().t()
+    if epi & 1:
+        v = v + bias.float()
+    if epi & ~1:
+        v = bf(v)
+    if epi & 2:
+        v = bf(torch.nn.functional.gelu(v, approximate="tanh"))
+    if epi & 4:
+        rows = torch.arange(a.shape[0], device=a.device) // rpb
+        v = bf(v * gate.float()[rows])
+    if epi & 16:
+        v = bf(v * scale)
+    if epi & 8:
+        v = v + res.float()
+    return v.to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (128, 256, 256), (300, 512, 512), (1000, 768, 1536), (77, 64, 128),
+                                   (4095, 1536, 512), (2, 512, 256)])
+def test_gemm_bias(ops, M, N, K):
+    a, w, b = _rand((M, K), 6), _rand((N, K), 7, 1 / math.sqrt(K)), _rand((N,), 8, 0.1)
+    out = ops.gemm(a, w, b)
+    assert relerr(out, _gemm_ref(a, w, b, 1)) < 4e-3
+    out0 = ops.gemm(a, w, None)
+    assert relerr(out0, _gemm_ref(a, w, None, 0)) < 4e-3
+
+
+@pytest.mark.parametrize("epi", [3, 9, 13, 25])
+def test_gemm_epilogues(ops, epi):
+    M, N, K, rpb = 650, 768, 512, 325  # a 128-row tile straddles the batch boundary at row 325
+    a, w, b = _rand((M, K), 9), _rand((N, K), 10, 1 / math.sqrt(K)), _rand((N,), 11, 0.1)
+    gate = _rand((2, 6, N), 12, 0.5)[:, 2]  # strided [B, N] view like m[:, 2]
+    res = _rand((M, N), 13)
+    out = ops.gemm(a, w, b, epilogue=epi, gate=gate if epi & 4 else None, rows_per_batch=rpb,
+                   residual=res if epi & 8 else None, scale=0.6)
+    ref = _gemm_ref(a, w, b, epi, gate, rpb, res, 0.6)
+    assert relerr(out, ref) < 4e-3
+
+
+def test_gemm_inplace_residual_and_strided_views(ops):
+    """x += scale * (c W^T + b) written over x (adapter accumulate) and A given as a column slice of a wider buffer."""
+    M, N, K = 500, 512, 256
+    wide = _rand((M, 3 * K), 14)
+    a = wide[:, K:2 * K]
+    w, b = _rand((N, K), 15, 1 / math.sqrt(K)), _rand((N,), 16, 0.1)
+    x = _rand((M, N), 17)
+    ref = _gemm_ref(a, w, b, 25, res=x.clone(), scale=1.0)
+    ops.gemm(a, w, b, epilogue=25, residual=x, scale=1.0, out=x)
+    assert relerr(x, ref) < 4e-3
+
+
+def test_gemm_large_k_many_tiles(ops):
+    M, N, K = 2048, 2048, 8960
+    a, w, b = _rand((M, K), 18), _rand((N, K), 19, 1 / math.sqrt(K)), _rand((N,), 20, 0.1)
+    assert relerr(ops.gemm(a, w, b), _gemm_ref(a, w, b, 1)) < 4e-3
+
+
+ATTN_SHAPES = [(1, 1, 128, 128), (2, 2, 256, 256), (2, 2, 333, 333), (1, 3, 1950, 1950), (2, 2, 333, 512),
+               (1, 2, 4095, 4095), (1, 1, 100, 37)]
+
+
+def _attn_case(ops, B, H, Lq, Lk, variant, fused):
+    d = 128
+    if fused and Lq == Lk:  # q/k/v as column slices of one [B*L, 3*H*d] buffer, like the fused QKV GEMM output
+        buf = _rand((B * Lq, 3 * H * d), 21)
+        q, k, v = (buf[:, i * H * d:(i + 1) * H * d].view(B, Lq, H, d) for i in range(3))
+    else:
+        q, k, v = _rand((B, Lq, H, d), 22), _rand((B, Lk, H, d), 23), _rand((B, Lk, H, d), 24)
+    out = ops.flash_attn(q, k, v, variant=variant)
+    ref = restate.sdpa(q, k, v)
+    torch.cuda.synchronize()
+    return relerr(out, ref)
+
+
+@pytest.mark.parametrize("B,H,Lq,Lk", ATTN_SHAPES)
+@pytest.mark.parametrize("fused", [False, True])
+def test_flash_attn_smem_p(ops, B, H, Lq, Lk, fused):
+    assert _attn_case(ops, B, H, Lq, Lk, 0, fused) < 1e-2
+
+
+@pytest.mark.parametrize("B,H,Lq,Lk", ATTN_SHAPES)
+def test_flash_attn_tmem_p(ops, B, H, Lq, Lk):
+    assert _attn_case(ops, B, H, Lq, Lk, 1, True) < 1e-2
+
+
+def test_flash_attn_large_scores_rescale(ops):
+    """Rows whose running max keeps growing across key tiles exercise the O rescale path."""
+    B, H, L, d = 1, 1, 1024, 128
+    q = _rand((B, L, H, d), 25, 3.0)
+    k = _rand((B, L, H, d), 26, 1.0)
+    k = (k.float() * torch.linspace(0.2, 3.0, L, device="cuda")[None, :, None, None]).to(torch.bfloat16)
+    v = _rand((B, L, H, d), 27)
+    for variant in (0,):
+        assert relerr(ops.flash_attn(q, k, v, variant=variant), restate.sdpa(q, k, v)) < 1e-2
+
+
+def test_patchify_unpatchify(ops):
+    u = _rand((12, 3, 8, 10), 28)
+    got = ops.patchify(u)
+    assert torch.equal(got, restate.patchify(u))
+    y = _rand((3 * 4 * 5, 64), 29)
+    assert torch.equal(ops.unpatchify(y, (3, 4, 5)), restate.unpatchify(y, (3, 4, 5)))
+
+
+def test_errors_are_reported(ops):
+    from versecrafter_b200 import _lib
+    a, w = _rand((16, 60), 30), _rand((64, 60), 31)
+    with pytest.raises(_lib.VCError):
+        ops.gemm(a, w, None)  # K % 8 != 0
+    with pytest.raises(_lib.VCError):
+        ops.gemm(a.cpu(), w.cpu(), None)  # no CPU fallback

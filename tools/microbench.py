@@ -1,0 +1,123 @@
+"""Per-kernel timing on one B200 (CUDA events, warm-up, L2 flushed between iterations by working sets > L2).
+Writes JSON lines to gpurun_out/microbench.jsonl.  Library baselines (torch.matmul = cuBLASLt, flash_attn 2.8) are
+timed beside each kernel as the bar to beat; they are not on the product path."""
+import json
+import math
+import os
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from versecrafter_b200 import ops  # noqa: E402
+
+PEAKS = {"hbm_gbs": 6548.5, "bf16_tflops": 1604.8, "bf16_tflops_sustained": 1381.2}
+try:
+    PEAKS.update(json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json"))))
+except Exception:
+    pass
+OUT = os.path.join(os.path.dirname(__file__), "..", "gpurun_out", "microbench.jsonl")
+
+
+def timeit(fn, iters=10, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(iters + 1)]
+    ev[0].record()
+    for i in range(iters):
+        fn()
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ts = [ev[i].elapsed_time(ev[i + 1]) for i in range(iters)]
+    return sum(ts) / len(ts), min(ts)
+
+
+def emit(rec):
+    print(json.dumps(rec), flush=True)
+    with open(OUT, "a") as f:
+        f.write(json.dumps(rec) + "\n")
+
+
+def rel(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm())
+
+
+def bench_rows(B=2, L=32760, D=5120):
+    x = torch.randn(B, L, D, device="cuda", dtype=torch.bfloat16)
+    m = torch.randn(B, 6, D, device="cuda", dtype=torch.bfloat16) * 0.1
+    out = torch.empty_like(x)
+    avg, mn = timeit(lambda: ops.ln_modulate(x, m[:, 0], m[:, 1], L, out=out))
+    bytes_ = 2 * x.numel() * 2
+    emit(dict(kernel="ln_modulate", shape=[B, L, D], ms=avg, ms_min=mn, gbs=bytes_ / avg / 1e6,
+              frac_hbm=bytes_ / avg / 1e6 / PEAKS["hbm_gbs"]))
+    del out
+    qkv = torch.randn(B * L, 3 * D, device="cuda", dtype=torch.bfloat16)
+    g = torch.ones(D, device="cuda", dtype=torch.bfloat16)
+    grid = (21, 30, 52) if L == 32760 else (1, 1, L)
+    rope = ops.rope_table(128, grid, "cuda")
+    avg, mn = timeit(lambda: ops.rmsnorm_rope_(qkv, D, 2, g, g, L, rope=rope, grid=grid))
+    bytes_ = 2 * 2 * B * L * D * 2
+    emit(dict(kernel="rmsnorm_rope_qk", shape=[B * L, 3 * D], ms=avg, ms_min=mn, gbs=bytes_ / avg / 1e6,
+              frac_hbm=bytes_ / avg / 1e6 / PEAKS["hbm_gbs"]))
+
+
+def bench_gemm(M, N, K, epi="bias"):
+    a = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16) / math.sqrt(K)
+    b = torch.randn(N, device="cuda", dtype=torch.bfloat16)
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    kw = {}
+    if epi == "gelu":
+        kw = dict(epilogue=3)
+    elif epi == "gate_res":
+        gate = torch.randn(2, N, device="cuda", dtype=torch.bfloat16)
+        res = torch.randn(M, N, device="cuda", dtype=torch.bfloat16)
+        kw = dict(epilogue=13, gate=gate, rows_per_batch=(M + 1) // 2, residual=res)
+    avg, mn = timeit(lambda: ops.gemm(a, w, b, out=out, **kw), iters=6)
+    flops = 2.0 * M * N * K
+    ref_avg, ref_mn = timeit(lambda: torch.nn.functional.linear(a, w, b), iters=6)
+    err = rel(ops.gemm(a[:4096], w, b), torch.nn.functional.linear(a[:4096], w, b)) if epi == "bias" else None
+    emit(dict(kernel="gemm_" + epi, shape=[M, N, K], ms=avg, ms_min=mn, tflops=flops / avg / 1e9,
+              frac_bf16_sustained=flops / avg / 1e9 / PEAKS["bf16_tflops_sustained"],
+              frac_bf16_burst=flops / mn / 1e9 / PEAKS["bf16_tflops"],
+              cublas_ms=ref_avg, cublas_tflops=flops / ref_avg / 1e9, rel_err_vs_cublas=err))
+
+
+def bench_attn(B, H, Lq, Lk, variant):
+    q = torch.randn(B, Lq, H, 128, device="cuda", dtype=torch.bfloat16)
+    k = torch.randn(B, Lk, H, 128, device="cuda", dtype=torch.bfloat16)
+    v = torch.randn(B, Lk, H, 128, device="cuda", dtype=torch.bfloat16)
+    out = torch.empty_like(q)
+    avg, mn = timeit(lambda: ops.flash_attn(q, k, v, out=out, variant=variant), iters=5, warmup=2)
+    flops = 4.0 * B * H * Lq * Lk * 128
+    rec = dict(kernel=f"flash_attn_v{variant}", shape=[B, H, Lq, Lk], ms=avg, ms_min=mn, tflops=flops / avg / 1e9,
+               frac_bf16_sustained=flops / avg / 1e9 / PEAKS["bf16_tflops_sustained"])
+    try:
+        from flash_attn import flash_attn_func
+        ref = flash_attn_func(q, k, v)
+        rec["rel_err_vs_fa2"] = rel(out, ref)
+        ravg, _ = timeit(lambda: flash_attn_func(q, k, v), iters=5, warmup=2)
+        rec["fa2_ms"] = ravg
+        rec["fa2_tflops"] = flops / ravg / 1e9
+    except Exception as e:  # noqa: BLE001
+        rec["fa2_error"] = repr(e)[:200]
+    emit(rec)
+
+
+if __name__ == "__main__":
+    os.makedirs(os.path.dirname(OUT), exist_ok=True)
+    which = sys.argv[1:] or ["rows", "gemm", "attn"]
+    torch.cuda.init()
+    if "rows" in which:
+        bench_rows()
+    if "gemm" in which:
+        M = 65520
+        for (N, K, epi) in [(15360, 5120, "bias"), (5120, 5120, "gate_res"), (13824, 5120, "gelu"), (5120, 13824, "gate_res"),
+                            (5120, 512, "bias"), (4608, 1536, "bias")]:
+            bench_gemm(M, N, K, epi)
+    if "attn" in which:
+        for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "0,1").split(",")]:
+            bench_attn(1, 8, 32760, 32760, variant)
+            bench_attn(2, 40, 32760, 512, variant)

@@ -1,0 +1,359 @@
+// Non-causal flash attention forward, head_dim 128, bf16 in/out, fp32 softmax state, on tcgen05 tensor cores with
+// TMEM-resident S / O accumulators (SURVEY.md §2.2 K6 self-attention, K7 cross-attention).
+// Replaces videox_fun attention() at wan_transformer3d.py:394-399 and :425-430:  softmax(Q K^T / sqrt(d)) V,
+// keys beyond Lk masked (TMA zero-fills the tail; the last key tile is masked to -inf before the row max).
+//
+// One CTA = one (batch, head, 256 query rows) = two 128-row Q tiles that ping-pong on the tensor pipe:
+//   warp 0      TMA producer: Q once, then K_0,V_0,K_1,V_1,... through an mbarrier ring of 32 KB slots
+//   warp 1      one elected thread issues every tcgen05.mma:  S_q = Q_q K_j^T   (M=128,N=128,K=128)
+//                                                              O_q += P_q V_j   (M=128,N=128,K=128, V MN-major)
+//   warp 2      TMEM allocator (512 columns: S0 | S1 | O0 | O1)
+//   warps 4-7   softmax of Q tile 0 (thread = query row = TMEM lane), warps 8-11 the same for Q tile 1:
+//               tcgen05.ld S row -> running max (lazy rescale, threshold 2^8) -> exp2 -> P (bf16)
+//               P goes to shared memory (kPInTmem=false, SS MMA) or back into TMEM over S (kPInTmem=true, TS MMA)
+// Issue order  S0_0 S1_0 | PV0_0 S0_1 | PV1_0 S1_1 | PV0_1 S0_2 | ...  so that the softmax of one Q tile runs while
+// the tensor pipe works on the other.  tcgen05 ops of one thread retire in order, so "S_q,j+1 done" implies
+// "PV_q,j done": that single s_full barrier also guards the O_q rescale and the reuse of the P_q buffer.
+#include "common.cuh"
+
+namespace {
+
+constexpr int HD = 128;        // head dim
+constexpr int BQ = 128;        // rows per Q tile (2 tiles per CTA)
+constexpr int BKV = 128;       // keys per tile
+constexpr int HALF_BYTES = 128 * 128;          // 128 rows x 64 bf16 (one 128B-swizzle column block) = 16 KB
+constexpr int TILE_BYTES = 2 * HALF_BYTES;     // 32 KB
+constexpr int NUM_THREADS = 384;
+constexpr float RESCALE_THRESHOLD = 8.0f;      // log2 units
+
+template <bool kPInTmem>
+struct Cfg {
+  static constexpr int NSLOT = kPInTmem ? 5 : 3;
+  static constexpr int P_BYTES = kPInTmem ? 0 : 2 * TILE_BYTES;
+  static constexpr int SMEM_BYTES = 2 * TILE_BYTES + NSLOT * TILE_BYTES + P_BYTES + 256 + 1024;
+};
+
+struct AttnParams {
+  __nv_bfloat16* O;
+  long long o_stride_b, o_stride_l, o_stride_h;  // elements
+  int Lq, Lk;
+  float scale_log2;  // softmax_scale * log2(e)
+};
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;\n" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <bool kPInTmem>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+flash_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                  const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+  using C = Cfg<kPInTmem>;
+  constexpr int NSLOT = C::NSLOT;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;                                   // 2 tiles
+  uint8_t* sKV = smem + 2 * TILE_BYTES;                 // NSLOT tiles
+  uint8_t* sP = sKV + NSLOT * TILE_BYTES;               // 2 tiles (SS variant only)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + C::P_BYTES);
+  uint64_t* q_full = bars;            // 1
+  uint64_t* kv_full = bars + 1;       // NSLOT
+  uint64_t* kv_empty = kv_full + NSLOT;
+  uint64_t* s_full = kv_empty + NSLOT;  // 2
+  uint64_t* p_ready = s_full + 2;       // 2
+  uint64_t* o_full = p_ready + 2;       // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int q_blk = blockIdx.x, head = blockIdx.y, batch = blockIdx.z;
+  const int nk = (p.Lk + BKV - 1) / BKV;
+
+  if (threadIdx.x == 0) {
+    vc::mbar_init(q_full, 1);
+    for (int i = 0; i < NSLOT; ++i) {
+      vc::mbar_init(&kv_full[i], 1);
+      vc::mbar_init(&kv_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      vc::mbar_init(&s_full[i], 1);
+      vc::mbar_init(&p_ready[i], 128);
+      vc::mbar_init(&o_full[i], 1);
+    }
+    vc::fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    vc::tma_prefetch_desc(&tmQ);
+    vc::tma_prefetch_desc(&tmK);
+    vc::tma_prefetch_desc(&tmV);
+  }
+  if (warp == 2) vc::tmem_alloc(tmem_slot, 512);
+  vc::tc_fence_before();
+  __syncthreads();
+  vc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < 4) {
+    vc::reg_dealloc<56>();
+    if (warp == 0) {
+      // ---------------------------------------------------------------- TMA producer
+      if (vc::elect_one()) {
+        vc::mbar_expect_tx(q_full, 2 * TILE_BYTES);
+#pragma unroll
+        for (int qt = 0; qt < 2; ++qt)
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            vc::tma_load_4d(sQ + qt * TILE_BYTES + h * HALF_BYTES, &tmQ, q_full, h * 64, (q_blk * 2 + qt) * BQ, head,
+                            batch);
+        for (int idx = 0; idx < 2 * nk; ++idx) {
+          const int slot = idx % NSLOT;
+          const uint32_t ph = (idx / NSLOT) & 1;
+          vc::mbar_wait(&kv_empty[slot], ph ^ 1);
+          vc::mbar_expect_tx(&kv_full[slot], TILE_BYTES);
+          const CUtensorMap* tm = (idx & 1) ? &tmV : &tmK;
+          const int row0 = (idx >> 1) * BKV;
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            vc::tma_load_4d(sKV + slot * TILE_BYTES + h * HALF_BYTES, tm, &kv_full[slot], h * 64, row0, head, batch);
+        }
+      }
+    } else if (warp == 1) {
+      // ---------------------------------------------------------------- MMA issuer
+      if (vc::elect_one()) {
+        constexpr uint32_t idesc_s = vc::umma_idesc_bf16(BQ, BKV, 0, 0);  // Q (K-major) x K (K-major)
+        constexpr uint32_t idesc_o = vc::umma_idesc_bf16(BQ, HD, 0, 1);   // P (K-major) x V (MN-major)
+        auto kv_wait = [&](int idx) { vc::mbar_wait(&kv_full[idx % NSLOT], (idx / NSLOT) & 1); };
+        auto kv_addr = [&](int idx) { return vc::smem_u32(sKV + (idx % NSLOT) * TILE_BYTES); };
+        auto issue_s = [&](int q, int j) {
+          const uint32_t qa = vc::smem_u32(sQ + q * TILE_BYTES);
+          const uint32_t ka = kv_addr(2 * j);
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k) {
+            const uint32_t off = (k >> 2) * HALF_BYTES + (k & 3) * 32;
+            vc::umma_ss(tmem_base + q * 128, vc::umma_desc_sw128(qa + off, 16, 1024),
+                        vc::umma_desc_sw128(ka + off, 16, 1024), idesc_s, k != 0 ? 1u : 0u);
+          }
+          vc::umma_commit(&s_full[q]);
+        };
+        auto issue_pv = [&](int q, int j) {
+          const uint32_t va = kv_addr(2 * j + 1);
+          const uint32_t d_tmem = tmem_base + 256 + q * 128;
+#pragma unroll
+          for (int k = 0; k < BKV / 16; ++k) {
+            const uint64_t vdesc = vc::umma_desc_sw128(va + k * 2048, HALF_BYTES, 1024);
+            const uint32_t accum = (j != 0 || k != 0) ? 1u : 0u;
+            if (kPInTmem) {
+              vc::umma_ts(d_tmem, tmem_base + q * 128 + k * 8, vdesc, idesc_o, accum);
+            } else {
+              const uint32_t pa = vc::smem_u32(sP + q * TILE_BYTES) + (k >> 2) * HALF_BYTES + (k & 3) * 32;
+              vc::umma_ss(d_tmem, vc::umma_desc_sw128(pa, 16, 1024), vdesc, idesc_o, accum);
+            }
+          }
+        };
+        vc::mbar_wait(q_full, 0);
+        kv_wait(0);
+        vc::tc_fence_after();
+        issue_s(0, 0);
+        issue_s(1, 0);
+        vc::umma_commit(&kv_empty[0]);
+        for (int j = 0; j < nk; ++j) {
+          kv_wait(2 * j + 1);  // V_j
+          for (int q = 0; q < 2; ++q) {
+            vc::mbar_wait(&p_ready[q], j & 1);
+            vc::tc_fence_after();
+            issue_pv(q, j);
+            if (q == 1) vc::umma_commit(&kv_empty[(2 * j + 1) % NSLOT]);
+            if (j + 1 < nk) {
+              if (q == 0) {
+                kv_wait(2 * j + 2);  // K_{j+1}
+                vc::tc_fence_after();
+              }
+              issue_s(q, j + 1);
+              if (q == 1) vc::umma_commit(&kv_empty[(2 * j + 2) % NSLOT]);
+            } else {
+              vc::umma_commit(&o_full[q]);
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ softmax + correction + epilogue
+    vc::reg_alloc<208>();
+    const int q = (warp - 4) >> 2;          // Q tile of this warpgroup
+    const int quarter = warp & 3;           // TMEM lane quarter this warp may touch
+    const int row = quarter * 32 + lane;    // row inside the Q tile == TMEM lane
+    const uint32_t lane_bits = static_cast<uint32_t>(quarter * 32) << 16;
+    const uint32_t s_addr = tmem_base + q * 128 + lane_bits;
+    const uint32_t o_addr = tmem_base + 256 + q * 128 + lane_bits;
+    const float sl2 = p.scale_log2;
+    float m_run = -INFINITY;  // running (possibly stale) row max, raw score units
+    float l_run = 0.f;
+    uint8_t* p_row = sP + q * TILE_BYTES + row * 128;
+
+    for (int j = 0; j < nk; ++j) {
+      vc::mbar_wait(&s_full[q], j & 1);
+      vc::tc_fence_after();
+      uint32_t s[128];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) vc::tmem_ld32(s_addr + c * 32, s + c * 32);
+      vc::tmem_ld_wait();
+      if (j == nk - 1) {
+        const int valid = p.Lk - j * BKV;
+        if (valid < BKV) {
+#pragma unroll
+          for (int i = 0; i < 128; ++i)
+            if (i >= valid) s[i] = __float_as_uint(-INFINITY);
+        }
+      }
+      float mt = __uint_as_float(s[0]);
+#pragma unroll
+      for (int i = 1; i < 128; ++i) mt = fmaxf(mt, __uint_as_float(s[i]));
+      const float m_new = fmaxf(m_run, mt);
+      const bool need = (m_new - m_run) * sl2 > RESCALE_THRESHOLD;  // true on the first tile (m_run = -inf)
+      if (__any_sync(0xffffffffu, need)) {
+        const float alpha = fast_exp2((m_run - m_new) * sl2);
+        l_run *= alpha;
+        m_run = m_new;
+        if (j > 0) {
+          // O_q is idle here: S_q,j done implies PV_q,j-1 done, and PV_q,j waits for our p_ready arrival
+#pragma unroll 1
+          for (int c = 0; c < 4; ++c) {
+            uint32_t o[32];
+            vc::tmem_ld32(o_addr + c * 32, o);
+            vc::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            vc::tmem_st32(o_addr + c * 32, o);
+          }
+          vc::tmem_st_wait();
+        }
+      }
+      const float mb = m_run * sl2;
+      float sum = 0.f;
+      if (kPInTmem) {
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+          const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -mb));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -mb));
+          sum += p0 + p1;
+          s[i] = vc::pack_bf16x2(p0, p1);
+        }
+        vc::tmem_st32(s_addr, s);
+        vc::tmem_st32(s_addr + 32, s + 32);
+        vc::tmem_st_wait();
+        l_run += sum;
+        vc::tc_fence_before();
+      } else {
+#pragma unroll
+        for (int ch = 0; ch < 16; ++ch) {  // 8 keys = one 16-byte chunk of the swizzled K-major P tile
+          float pv[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            pv[i] = fast_exp2(fmaf(__uint_as_float(s[ch * 8 + i]), sl2, -mb));
+            sum += pv[i];
+          }
+          uint4 u;
+          u.x = vc::pack_bf16x2(pv[0], pv[1]);
+          u.y = vc::pack_bf16x2(pv[2], pv[3]);
+          u.z = vc::pack_bf16x2(pv[4], pv[5]);
+          u.w = vc::pack_bf16x2(pv[6], pv[7]);
+          const int half = ch >> 3, chunk = ch & 7;
+          *reinterpret_cast<uint4*>(p_row + half * HALF_BYTES + ((chunk ^ (row & 7)) << 4)) = u;
+        }
+        l_run += sum;
+        vc::fence_proxy_async_smem();
+      }
+      vc::mbar_arrive(&p_ready[q]);
+    }
+
+    // epilogue: O_q / l -> bf16 -> global
+    vc::mbar_wait(&o_full[q], 0);
+    vc::tc_fence_after();
+    const float inv_l = 1.0f / l_run;
+    const int q_row = (q_blk * 2 + q) * BQ + row;
+    __nv_bfloat16* orow = p.O + (long long)batch * p.o_stride_b + (long long)q_row * p.o_stride_l +
+                          (long long)head * p.o_stride_h;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t o[32];
+      vc::tmem_ld32(o_addr + c * 32, o);
+      vc::tmem_ld_wait();
+      if (q_row < p.Lq) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 u;
+          u.x = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 0]) * inv_l, __uint_as_float(o[g * 8 + 1]) * inv_l);
+          u.y = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 2]) * inv_l, __uint_as_float(o[g * 8 + 3]) * inv_l);
+          u.z = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 4]) * inv_l, __uint_as_float(o[g * 8 + 5]) * inv_l);
+          u.w = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 6]) * inv_l, __uint_as_float(o[g * 8 + 7]) * inv_l);
+          *reinterpret_cast<uint4*>(orow + c * 32 + g * 8) = u;
+        }
+      }
+    }
+  }
+
+  vc::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) vc::tmem_dealloc(tmem_base, 512);
+}
+
+int make_qkv_map(CUtensorMap* tm, const void* base, int B, int H, int L, long long sb, long long sl, long long sh) {
+  uint64_t dims[4] = {(uint64_t)HD, (uint64_t)L, (uint64_t)H, (uint64_t)B};
+  uint64_t strides[3] = {(uint64_t)sl * 2, (uint64_t)sh * 2, (uint64_t)sb * 2};
+  uint32_t box[4] = {64, 128, 1, 1};
+  return vc_host::make_tmap_bf16(tm, base, 4, dims, strides, box);
+}
+
+template <bool kPInTmem>
+int launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p, dim3 grid,
+           cudaStream_t s) {
+  static bool attr_set = false;
+  constexpr int smem = Cfg<kPInTmem>::SMEM_BYTES;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(flash_attn_kernel<kPInTmem>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      vc_host::set_error("vc_flash_attn_fwd: cannot set %d B dynamic smem: %s", smem, cudaGetErrorString(e));
+      return (int)e;
+    }
+    attr_set = true;
+  }
+  flash_attn_kernel<kPInTmem><<<grid, NUM_THREADS, smem, s>>>(tq, tk, tv, p);
+  return 0;
+}
+
+}  // namespace
+
+// strides are in ELEMENTS: (batch, token, head); the head_dim axis must be contiguous (stride 1), head_dim == 128.
+extern "C" int vc_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, int B, int H, int Lq, int Lk,
+                                 int head_dim, const long long* q_strides, const long long* k_strides,
+                                 const long long* v_strides, const long long* o_strides, float softmax_scale,
+                                 int variant, void* stream) {
+  VC_CHECK_ARG(q && k && v && o && q_strides && k_strides && v_strides && o_strides, "vc_flash_attn_fwd: null pointer");
+  VC_CHECK_ARG(head_dim == HD, "vc_flash_attn_fwd: head_dim %d unsupported (only 128)", head_dim);
+  VC_CHECK_ARG(B > 0 && H > 0 && Lq >= 0 && Lk > 0, "vc_flash_attn_fwd: bad sizes B=%d H=%d Lq=%d Lk=%d", B, H, Lq, Lk);
+  VC_CHECK_ARG(variant == 0 || variant == 1, "vc_flash_attn_fwd: variant must be 0 (P in smem) or 1 (P in TMEM)");
+  const long long* all[4] = {q_strides, k_strides, v_strides, o_strides};
+  for (int t = 0; t < 4; ++t)
+    for (int i = 0; i < 3; ++i)
+      VC_CHECK_ARG(all[t][i] % 8 == 0 && all[t][i] > 0, "vc_flash_attn_fwd: strides must be positive multiples of 8 elements");
+  VC_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) % 16 == 0, "vc_flash_attn_fwd: 16-byte alignment");
+  if (Lq == 0) return 0;
+  CUtensorMap tq, tk, tv;
+  int rc;
+  if ((rc = make_qkv_map(&tq, q, B, H, Lq, q_strides[0], q_strides[1], q_strides[2]))) return rc;
+  if ((rc = make_qkv_map(&tk, k, B, H, Lk, k_strides[0], k_strides[1], k_strides[2]))) return rc;
+  if ((rc = make_qkv_map(&tv, v, B, H, Lk, v_strides[0], v_strides[1], v_strides[2]))) return rc;
+  AttnParams p;
+  p.O = (__nv_bfloat16*)o;
+  p.o_stride_b = o_strides[0]; p.o_stride_l = o_strides[1]; p.o_stride_h = o_strides[2];
+  p.Lq = Lq; p.Lk = Lk;
+  p.scale_log2 = softmax_scale * 1.4426950408889634f;
+  dim3 grid((Lq + 2 * BQ - 1) / (2 * BQ), H, B);
+  rc = variant ? launch<true>(tq, tk, tv, p, grid, (cudaStream_t)stream)
+               : launch<false>(tq, tk, tv, p, grid, (cudaStream_t)stream);
+  if (rc) return rc;
+  VC_RETURN_LAUNCH_STATUS("vc_flash_attn_fwd");
+}

@@ -1,0 +1,326 @@
+// bf16 GEMM  C[M,N] = epilogue(A[M,K] . W[N,K]^T)  on tcgen05 tensor cores (SURVEY.md §2.2 K8/K9/K10, K1/K2 after
+// patchify).  Replaces every nn.Linear on the hot path (wan_transformer3d.py:366-369, :557-559; after_proj /
+// before_proj wan_transformer3d_versecrafter.py:105-121; Conv3d patch embeddings :199-201, wan_transformer3d.py:758).
+//
+// Persistent, warp-specialised, one CTA per SM:
+//   warp 0   : TMA producer  (A tile 128x64, W tile 256x64, 128B swizzle, 4-stage mbarrier ring)
+//   warp 1   : one elected thread issues tcgen05.mma M=128 N=256 K=16 (4 per k-block), fp32 accumulators in TMEM
+//   warp 2   : TMEM allocator (512 columns = 2 accumulator stages of 256) + epilogue
+//   warps 2-5: epilogue: tcgen05.ld 32 columns at a time -> bias / GELU-tanh / gate / scale / residual -> bf16 global
+// The accumulator is double-buffered in TMEM so tile i's epilogue overlaps tile i+1's main loop.
+// Epilogue rounding points follow the reference's op-by-op bf16 arithmetic.
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128, BN = 256, BK = 64, STAGES = 4;
+constexpr int A_BYTES = BM * BK * 2;  // 16 KB
+constexpr int B_BYTES = BN * BK * 2;  // 32 KB
+constexpr int BAR_BYTES = 256;
+constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + BAR_BYTES + 1024;  // +1024 for manual alignment
+constexpr int GROUP_M = 16;
+constexpr int NUM_THREADS = 192;
+
+enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16 };
+
+struct GemmParams {
+  long long M, N, K;
+  __nv_bfloat16* C;
+  long long ldc;
+  const __nv_bfloat16* bias;      // [N]
+  const __nv_bfloat16* gate;      // [batch, N] rows gate_stride apart
+  long long gate_stride;
+  long long rows_per_batch;
+  const __nv_bfloat16* residual;  // [M, N] rows ldr apart (may alias C)
+  long long ldr;
+  float scale;
+  int m_tiles, n_tiles;
+};
+
+__device__ __forceinline__ void tile_coords(int t, int m_tiles, int n_tiles, int& m, int& n) {
+  const int per_group = GROUP_M * n_tiles;
+  const int g = t / per_group;
+  const int r = t - g * per_group;
+  const int m0 = g * GROUP_M;
+  const int gm = min(GROUP_M, m_tiles - m0);
+  m = m0 + r % gm;
+  n = r / gm;
+}
+
+__device__ __forceinline__ float gelu_tanh(float x) {
+  // 0.5 x (1 + tanh(sqrt(2/pi) (x + 0.044715 x^3)));  tanh(u) = 1 - 2 / (1 + exp(2u))
+  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+  const float t = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * u));
+  return 0.5f * x * (1.0f + t);
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * (A_BYTES + B_BYTES));
+  uint64_t* empty = full + STAGES;
+  uint64_t* acc_full = empty + STAGES;
+  uint64_t* acc_empty = acc_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      vc::mbar_init(&full[i], 1);
+      vc::mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      vc::mbar_init(&acc_full[i], 1);
+      vc::mbar_init(&acc_empty[i], 128);
+    }
+    vc::fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    vc::tma_prefetch_desc(&tmA);
+    vc::tma_prefetch_desc(&tmB);
+  }
+  if (warp == 2) vc::tmem_alloc(tmem_slot, 512);
+  vc::tc_fence_before();
+  __syncthreads();
+  vc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_tiles = p.m_tiles * p.n_tiles;
+  const int k_blocks = (int)((p.K + BK - 1) / BK);
+
+  if (warp == 0) {
+    // ------------------------------------------------ TMA producer
+    if (vc::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        int m, n;
+        tile_coords(t, p.m_tiles, p.n_tiles, m, n);
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          vc::mbar_wait(&empty[stage], phase ^ 1);
+          vc::mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
+          vc::tma_load_2d(sA + stage * A_BYTES, &tmA, &full[stage], kb * BK, m * BM);
+          vc::tma_load_2d(sB + stage * B_BYTES, &tmB, &full[stage], kb * BK, n * BN);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------ MMA issuer
+    if (vc::elect_one()) {
+      constexpr uint32_t idesc = vc::umma_idesc_bf16(BM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        vc::mbar_wait(&acc_empty[acc], acc_phase ^ 1);
+        vc::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          vc::mbar_wait(&full[stage], phase);
+          vc::tc_fence_after();
+          const uint32_t a0 = vc::smem_u32(sA + stage * A_BYTES);
+          const uint32_t b0 = vc::smem_u32(sB + stage * B_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            vc::umma_ss(d_tmem, vc::umma_desc_sw128(a0 + k * 32, 16, 1024), vc::umma_desc_sw128(b0 + k * 32, 16, 1024),
+                        idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          vc::umma_commit(&empty[stage]);  // frees the smem stage when these MMAs retire
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        vc::umma_commit(&acc_full[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ------------------------------------------------ epilogue (warps 2..5 -> TMEM lane quarters 2,3,0,1)
+    const int quarter = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      int m, n;
+      tile_coords(t, p.m_tiles, p.n_tiles, m, n);
+      vc::mbar_wait(&acc_full[acc], acc_phase);
+      vc::tc_fence_after();
+      const long long row = (long long)m * BM + quarter * 32 + lane;
+      const bool row_ok = row < p.M;
+      __nv_bfloat16* crow = p.C + row * p.ldc;
+      const __nv_bfloat16* rrow = (EPI & EPI_RES) ? p.residual + row * p.ldr : nullptr;
+      const __nv_bfloat16* grow =
+          (EPI & EPI_GATE) ? p.gate + (row_ok ? row / p.rows_per_batch : 0) * p.gate_stride : nullptr;
+      const uint32_t t_addr = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        vc::tmem_ld32(t_addr + c * 32, r);
+        vc::tmem_ld_wait();
+        const long long col0 = (long long)n * BN + c * 32;
+        if (row_ok && col0 < p.N) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {  // 8 columns = one 16-byte store
+            const long long col = col0 + g * 8;
+            if (col < p.N) {
+              float v[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+              if (EPI & EPI_BIAS) {
+                const uint4 bu = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
+                const float2 b0 = vc::unpack_bf16x2(bu.x), b1 = vc::unpack_bf16x2(bu.y), b2 = vc::unpack_bf16x2(bu.z),
+                             b3 = vc::unpack_bf16x2(bu.w);
+                v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
+                v[4] += b2.x; v[5] += b2.y; v[6] += b3.x; v[7] += b3.y;
+              }
+              if (EPI & (EPI_GELU | EPI_GATE | EPI_RES | EPI_SCALE)) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = vc::bf16_round(v[j]);  // the Linear's own bf16 output
+              }
+              if (EPI & EPI_GELU) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
+              }
+              if (EPI & EPI_GATE) {
+                const uint4 gu = __ldg(reinterpret_cast<const uint4*>(grow + col));
+                const float2 g0 = vc::unpack_bf16x2(gu.x), g1 = vc::unpack_bf16x2(gu.y), g2 = vc::unpack_bf16x2(gu.z),
+                             g3 = vc::unpack_bf16x2(gu.w);
+                v[0] *= g0.x; v[1] *= g0.y; v[2] *= g1.x; v[3] *= g1.y;
+                v[4] *= g2.x; v[5] *= g2.y; v[6] *= g3.x; v[7] *= g3.y;
+              }
+              if (EPI & EPI_SCALE) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] *= p.scale;
+              }
+              if (EPI & EPI_RES) {
+                const uint4 ru = *reinterpret_cast<const uint4*>(rrow + col);
+                const float2 r0 = vc::unpack_bf16x2(ru.x), r1 = vc::unpack_bf16x2(ru.y), r2 = vc::unpack_bf16x2(ru.z),
+                             r3 = vc::unpack_bf16x2(ru.w);
+                if (EPI & (EPI_GATE | EPI_SCALE)) {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) v[j] = vc::bf16_round(v[j]);  // y*gate (or hint*scale) rounds first
+                }
+                v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
+                v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
+              }
+              uint4 o;
+              o.x = vc::pack_bf16x2(v[0], v[1]);
+              o.y = vc::pack_bf16x2(v[2], v[3]);
+              o.z = vc::pack_bf16x2(v[4], v[5]);
+              o.w = vc::pack_bf16x2(v[6], v[7]);
+              *reinterpret_cast<uint4*>(crow + col) = o;
+            }
+          }
+        }
+      }
+      vc::tc_fence_before();
+      vc::mbar_arrive(&acc_empty[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  vc::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) vc::tmem_dealloc(tmem_base, 512);
+}
+
+template <int EPI>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) {
+      vc_host::set_error("vc_gemm_bf16: cannot set %d B dynamic smem: %s", SMEM_BYTES, cudaGetErrorString(e));
+      return (int)e;
+    }
+    attr_set = true;
+  }
+  gemm_bf16_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, s>>>(ta, tb, p);
+  return 0;
+}
+
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+}  // namespace
+
+extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long long ldw, void* C, long long ldc,
+                            long long M, long long N, long long K, int epilogue, const void* bias, const void* gate,
+                            long long gate_batch_stride, long long rows_per_batch, const void* residual,
+                            long long ldr, float scale, void* stream) {
+  VC_CHECK_ARG(A && W && C, "vc_gemm_bf16: null operand");
+  VC_CHECK_ARG(M >= 0 && N > 0 && K > 0, "vc_gemm_bf16: bad shape M=%lld N=%lld K=%lld", M, N, K);
+  VC_CHECK_ARG(N % 8 == 0 && K % 8 == 0, "vc_gemm_bf16: N and K must be multiples of 8 (N=%lld K=%lld)", N, K);
+  VC_CHECK_ARG(lda % 8 == 0 && ldw % 8 == 0 && ldc % 8 == 0 && lda >= K && ldw >= K && ldc >= N,
+               "vc_gemm_bf16: leading dimensions must be multiples of 8 elements and cover the row");
+  VC_CHECK_ARG((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(C)) % 16 == 0,
+               "vc_gemm_bf16: operands must be 16-byte aligned");
+  VC_CHECK_ARG(!(epilogue & EPI_BIAS) || bias, "vc_gemm_bf16: bias epilogue without bias");
+  VC_CHECK_ARG(!(epilogue & EPI_GATE) || (gate && rows_per_batch > 0), "vc_gemm_bf16: gate epilogue without gate");
+  VC_CHECK_ARG(!(epilogue & EPI_RES) || (residual && ldr % 8 == 0 && ldr >= N), "vc_gemm_bf16: residual epilogue without residual");
+  if (M == 0) return 0;
+
+  CUtensorMap ta, tb;
+  {
+    uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
+    uint64_t strides[1] = {(uint64_t)lda * 2};
+    uint32_t box[2] = {BK, BM};
+    int rc = vc_host::make_tmap_bf16(&ta, A, 2, dims, strides, box);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)K, (uint64_t)N};
+    uint64_t strides[1] = {(uint64_t)ldw * 2};
+    uint32_t box[2] = {BK, BN};
+    int rc = vc_host::make_tmap_bf16(&tb, W, 2, dims, strides, box);
+    if (rc) return rc;
+  }
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.C = (__nv_bfloat16*)C; p.ldc = ldc;
+  p.bias = (const __nv_bfloat16*)bias;
+  p.gate = (const __nv_bfloat16*)gate; p.gate_stride = gate_batch_stride;
+  p.rows_per_batch = rows_per_batch > 0 ? rows_per_batch : 1;
+  p.residual = (const __nv_bfloat16*)residual; p.ldr = ldr;
+  p.scale = scale;
+  p.m_tiles = (int)((M + BM - 1) / BM);
+  p.n_tiles = (int)((N + BN - 1) / BN);
+  const long long tiles = (long long)p.m_tiles * p.n_tiles;
+  const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc;
+  switch (epilogue) {
+    case 0: rc = launch<0>(ta, tb, p, grid, s); break;
+    case EPI_BIAS: rc = launch<EPI_BIAS>(ta, tb, p, grid, s); break;
+    case EPI_BIAS | EPI_GELU: rc = launch<EPI_BIAS | EPI_GELU>(ta, tb, p, grid, s); break;
+    case EPI_BIAS | EPI_RES: rc = launch<EPI_BIAS | EPI_RES>(ta, tb, p, grid, s); break;
+    case EPI_BIAS | EPI_GATE | EPI_RES: rc = launch<EPI_BIAS | EPI_GATE | EPI_RES>(ta, tb, p, grid, s); break;
+    case EPI_BIAS | EPI_SCALE | EPI_RES: rc = launch<EPI_BIAS | EPI_SCALE | EPI_RES>(ta, tb, p, grid, s); break;
+    default:
+      vc_host::set_error("vc_gemm_bf16: unsupported epilogue mask %d", epilogue);
+      return -1;
+  }
+  if (rc) return rc;
+  VC_RETURN_LAUNCH_STATUS("vc_gemm_bf16");
+}

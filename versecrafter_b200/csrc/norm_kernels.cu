@@ -1,0 +1,324 @@
+// HBM-bound row kernels of the DiT block:
+//   vc_ln_modulate     : out = LN(x) * (1 + scale[b]) + shift[b]   or   LN(x) * gamma + beta
+//                        reference: WanLayerNorm + modulate, wan_transformer3d.py:326-346, :591-592, :603-604, :600
+//   vc_rmsnorm_rope_qk : in place on the fused QKV rows: q,k <- RoPE(RMSNorm_D(q|k) * g)
+//                        reference: WanRMSNorm :307-323 (over the FULL hidden dim), rope_apply :143-172
+// One warp owns one row; the row lives in registers between the statistics pass and the write (one HBM read and
+// one HBM write per element), 16-byte vector accesses, warp-shuffle reductions, no shared memory.
+// bf16 rounding points follow the reference's op-by-op autocast arithmetic.
+#include "common.cuh"
+
+namespace {
+
+using vc::bf16_round;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ uint4 ld_stream(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];\n"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream(uint4* p, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};\n" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ void unpack8(const uint4& u, float* f) {
+  float2 a = vc::unpack_bf16x2(u.x), b = vc::unpack_bf16x2(u.y), c = vc::unpack_bf16x2(u.z), d = vc::unpack_bf16x2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 u;
+  u.x = vc::pack_bf16x2(f[0], f[1]); u.y = vc::pack_bf16x2(f[2], f[3]);
+  u.z = vc::pack_bf16x2(f[4], f[5]); u.w = vc::pack_bf16x2(f[6], f[7]);
+  return u;
+}
+
+// ----------------------------------------------------------------------------------------------------
+// LayerNorm (+ modulate | affine).  VPL = 16-byte vectors per lane (row length D <= VPL*32*8).
+// mode 0: out = bf(bf(bf(ln) * bf(1 + scale)) + shift), shift/scale bf16 [batch, D] (row stride mod_stride)
+// mode 1: out = bf(ln * gamma + beta)   (fp32 affine inside layer_norm, one rounding; gamma/beta bf16)
+// ----------------------------------------------------------------------------------------------------
+template <int VPL>
+__global__ void __launch_bounds__(256) ln_modulate_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out,
+                                                         const __nv_bfloat16* __restrict__ p0,  // shift | beta
+                                                         const __nv_bfloat16* __restrict__ p1,  // scale | gamma
+                                                         long long mod_stride, long long rows, long long rows_per_batch,
+                                                         int D, long long ldx, long long ldo, float eps, int mode) {
+  const int lane = threadIdx.x & 31;
+  const int nvec = D >> 3;
+  const long long warps_total = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += warps_total) {
+    const uint4* xr = reinterpret_cast<const uint4*>(x + row * ldx);
+    uint4 raw[VPL];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      int v = lane + 32 * i;
+      raw[i] = (v < nvec) ? ld_stream(xr + v) : make_uint4(0, 0, 0, 0);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      float f[8];
+      unpack8(raw[i], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += f[j];
+    }
+    const float mean = warp_sum(s) / (float)D;
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      if (lane + 32 * i < nvec) {
+        float f[8];
+        unpack8(raw[i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float d = f[j] - mean;
+          ss += d * d;
+        }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(ss) / (float)D + eps);
+    const long long b = row / rows_per_batch;
+    const uint4* q0 = reinterpret_cast<const uint4*>(p0 + (mode == 0 ? b * mod_stride : 0));
+    const uint4* q1 = reinterpret_cast<const uint4*>(p1 + (mode == 0 ? b * mod_stride : 0));
+    uint4* orow = reinterpret_cast<uint4*>(out + row * ldo);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      int v = lane + 32 * i;
+      if (v < nvec) {
+        float f[8], a[8], c[8];
+        unpack8(raw[i], f);
+        unpack8(__ldg(q0 + v), a);
+        unpack8(__ldg(q1 + v), c);
+        if (mode == 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float ln = bf16_round((f[j] - mean) * rstd);
+            float sc = bf16_round(1.0f + c[j]);
+            f[j] = bf16_round(ln * sc) + a[j];
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = (f[j] - mean) * rstd * c[j] + a[j];
+        }
+        st_stream(orow + v, pack8(f));
+      }
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------
+// QK RMSNorm (full hidden dim) + 3-axis RoPE, in place.  Each warp handles the q row then the k row of a token.
+// qkv row layout: [q(D) | k(D) | v(D)] with row stride ld (elements).  Pairs are adjacent elements (2j, 2j+1).
+// rope table: float2 (cos, sin) rows [F*nf | H*nh | W*nw] flattened: tab_f[f][nf], tab_h[h][nh], tab_w[w][nw].
+// token position = pos_offset + (row % rows_per_batch); (f,h,w) from the global position, w fastest.
+// Rows whose position >= F*H*W pass through un-rotated (reference :168).
+// ----------------------------------------------------------------------------------------------------
+template <int VPL>
+__global__ void __launch_bounds__(256) rmsnorm_rope_kernel(__nv_bfloat16* __restrict__ qkv, long long ld, long long rows,
+                                                          long long rows_per_batch, long long pos_offset, int D,
+                                                          const __nv_bfloat16* __restrict__ gq,
+                                                          const __nv_bfloat16* __restrict__ gk,
+                                                          const float2* __restrict__ tab, int Fg, int Hg, int Wg,
+                                                          int nf, int nh, int nw, float eps, int do_rope, int n_mats) {
+  const int lane = threadIdx.x & 31;
+  const int nvec = D >> 3;
+  const int half_d = nf + nh + nw;  // complex pairs per head (64)
+  const long long warps_total = (long long)gridDim.x * (blockDim.x >> 5);
+  const float2* tab_f = tab;
+  const float2* tab_h = tab + (long long)Fg * nf;
+  const float2* tab_w = tab_h + (long long)Hg * nh;
+  for (long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += warps_total) {
+    const long long pos = pos_offset + (row % rows_per_batch);
+    const bool rot = do_rope && pos < (long long)Fg * Hg * Wg;
+    int pw = 0, ph = 0, pf = 0;
+    if (rot) {
+      pw = (int)(pos % Wg);
+      ph = (int)((pos / Wg) % Hg);
+      pf = (int)(pos / ((long long)Wg * Hg));
+    }
+#pragma unroll 1
+    for (int which = 0; which < n_mats; ++which) {
+      uint4* xr = reinterpret_cast<uint4*>(qkv + row * ld + (long long)which * D);
+      const uint4* gr = reinterpret_cast<const uint4*>(which == 0 ? gq : gk);
+      uint4 raw[VPL];
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        int v = lane + 32 * i;
+        raw[i] = (v < nvec) ? *(xr + v) : make_uint4(0, 0, 0, 0);
+      }
+      float ss = 0.f;
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        float f[8];
+        unpack8(raw[i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss += f[j] * f[j];
+      }
+      const float r = bf16_round(rsqrtf(warp_sum(ss) / (float)D + eps));
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        int v = lane + 32 * i;
+        if (v < nvec) {
+          float f[8], g[8];
+          unpack8(raw[i], f);
+          unpack8(__ldg(gr + v), g);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = bf16_round(bf16_round(f[j] * r) * g[j]);
+          if (rot) {
+            const int j0 = ((v * 8) % (2 * half_d)) >> 1;  // first complex pair of this vector within its head
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+              int j = j0 + p;
+              float2 cs;
+              if (j < nf) cs = __ldg(tab_f + pf * nf + j);
+              else if (j < nf + nh) cs = __ldg(tab_h + ph * nh + (j - nf));
+              else cs = __ldg(tab_w + pw * nw + (j - nf - nh));
+              float a = f[2 * p], b = f[2 * p + 1];
+              f[2 * p] = a * cs.x - b * cs.y;
+              f[2 * p + 1] = a * cs.y + b * cs.x;
+            }
+          }
+          *(xr + v) = pack8(f);
+        }
+      }
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------
+// patchify: [C, F, H, W] bf16 (one sample) -> A[L, C*4] bf16, K ordered (c, ph, pw)  (SURVEY App. A.1).
+// Feeds the tcgen05 GEMM that implements the Conv3d patch embedding (stride == kernel, so it is a pure GEMM).
+// thread -> (token, c): reads two 4-byte pairs (rows 2h, 2h+1), writes 8 contiguous bytes.
+// ----------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) patchify_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                                      int C, int Fr, int H, int W, long long ld_out) {
+  const int Hp = H >> 1, Wp = W >> 1;
+  const long long L = (long long)Fr * Hp * Wp;
+  const long long total = L * C;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    // consecutive threads walk w' first (coalesced 4-byte reads along W), then c, then (f,h)
+    const int w = (int)(idx % Wp);
+    const long long t1 = idx / Wp;
+    const int c = (int)(t1 % C);
+    const long long fh = t1 / C;
+    const int h = (int)(fh % Hp);
+    const int f = (int)(fh / Hp);
+    const __nv_bfloat16* src = in + (((long long)c * Fr + f) * H + 2 * h) * W + 2 * w;
+    uint32_t r0 = *reinterpret_cast<const uint32_t*>(src);
+    uint32_t r1 = *reinterpret_cast<const uint32_t*>(src + W);
+    const long long tok = ((long long)f * Hp + h) * Wp + w;
+    *reinterpret_cast<uint2*>(out + tok * ld_out + (long long)c * 4) = make_uint2(r0, r1);
+  }
+}
+
+// unpatchify: y [L, 4*Co] bf16|f32-as-bf16 -> out [Co, F, 2H', 2W'] (wan_transformer3d.py:1127-1150)
+__global__ void __launch_bounds__(256) unpatchify_kernel(const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ out,
+                                                        int Co, int Fg, int Hg, int Wg, long long ldy) {
+  const long long total = (long long)Co * Fg * Hg * 2 * Wg * 2;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int X = (int)(idx % (2 * Wg));
+    long long t = idx / (2 * Wg);
+    const int Y = (int)(t % (2 * Hg));
+    t /= (2 * Hg);
+    const int f = (int)(t % Fg);
+    const int c = (int)(t / Fg);
+    const long long tok = ((long long)f * Hg + (Y >> 1)) * Wg + (X >> 1);
+    out[idx] = y[tok * ldy + ((Y & 1) * 2 + (X & 1)) * Co + c];
+  }
+}
+
+template <typename F>
+int dispatch_vpl(int D, F&& f) {
+  const int need = (D / 8 + 31) / 32;
+  if (need <= 1) return f(std::integral_constant<int, 1>{});
+  if (need <= 2) return f(std::integral_constant<int, 2>{});
+  if (need <= 4) return f(std::integral_constant<int, 4>{});
+  if (need <= 6) return f(std::integral_constant<int, 6>{});
+  if (need <= 8) return f(std::integral_constant<int, 8>{});
+  if (need <= 12) return f(std::integral_constant<int, 12>{});
+  if (need <= 20) return f(std::integral_constant<int, 20>{});
+  if (need <= 32) return f(std::integral_constant<int, 32>{});
+  return -1;
+}
+
+int grid_for_rows(long long rows, int warps_per_cta) {
+  long long ctas = (rows + warps_per_cta - 1) / warps_per_cta;
+  const long long cap = 148LL * 8;  // 8 resident 256-thread CTAs per SM
+  return (int)(ctas < cap ? (ctas < 1 ? 1 : ctas) : cap);
+}
+
+}  // namespace
+
+extern "C" {
+
+int vc_ln_modulate(const void* x, long long ldx, void* out, long long ldo, const void* shift_or_beta,
+                   const void* scale_or_gamma, long long mod_batch_stride, long long rows, long long rows_per_batch,
+                   int D, float eps, int mode, void* stream) {
+  VC_CHECK_ARG(x && out && shift_or_beta && scale_or_gamma, "vc_ln_modulate: null pointer");
+  VC_CHECK_ARG(D > 0 && D % 8 == 0 && D <= 8192, "vc_ln_modulate: D=%d must be a multiple of 8 and <= 8192", D);
+  VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && ldx % 8 == 0 && ldo % 8 == 0, "vc_ln_modulate: bad rows/strides");
+  VC_CHECK_ARG(mode == 0 || mode == 1, "vc_ln_modulate: mode must be 0 (modulate) or 1 (affine)");
+  if (rows == 0) return 0;
+  int rc = dispatch_vpl(D, [&](auto vpl) {
+    constexpr int V = decltype(vpl)::value;
+    ln_modulate_kernel<V><<<grid_for_rows(rows, 8), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)x, (__nv_bfloat16*)out, (const __nv_bfloat16*)shift_or_beta,
+        (const __nv_bfloat16*)scale_or_gamma, mod_batch_stride, rows, rows_per_batch, D, ldx, ldo, eps, mode);
+    return 0;
+  });
+  VC_CHECK_ARG(rc == 0, "vc_ln_modulate: unsupported D=%d", D);
+  VC_RETURN_LAUNCH_STATUS("vc_ln_modulate");
+}
+
+int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset, int D,
+                       int n_mats, const void* gain_q, const void* gain_k, const void* rope_table, int grid_f,
+                       int grid_h, int grid_w, int nf, int nh, int nw, float eps, int apply_rope, void* stream) {
+  VC_CHECK_ARG(n_mats == 1 || n_mats == 2, "vc_rmsnorm_rope_qk: n_mats must be 1 or 2");
+  VC_CHECK_ARG(qkv && gain_q && (n_mats == 1 || gain_k), "vc_rmsnorm_rope_qk: null pointer");
+  VC_CHECK_ARG(D > 0 && D % 8 == 0 && D <= 8192 && ld % 8 == 0 && ld >= (long long)n_mats * D, "vc_rmsnorm_rope_qk: bad D/ld");
+  VC_CHECK_ARG(!apply_rope || (rope_table && nf > 0 && nh > 0 && nw > 0 && (nf + nh + nw) % 4 == 0 &&
+                               D % (2 * (nf + nh + nw)) == 0),
+               "vc_rmsnorm_rope_qk: bad rope table split");
+  VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && pos_offset >= 0, "vc_rmsnorm_rope_qk: bad rows");
+  if (rows == 0) return 0;
+  int rc = dispatch_vpl(D, [&](auto vpl) {
+    constexpr int V = decltype(vpl)::value;
+    rmsnorm_rope_kernel<V><<<grid_for_rows(rows, 8), 256, 0, (cudaStream_t)stream>>>(
+        (__nv_bfloat16*)qkv, ld, rows, rows_per_batch, pos_offset, D, (const __nv_bfloat16*)gain_q,
+        (const __nv_bfloat16*)gain_k, (const float2*)rope_table, grid_f, grid_h, grid_w, nf, nh, nw, eps, apply_rope, n_mats);
+    return 0;
+  });
+  VC_CHECK_ARG(rc == 0, "vc_rmsnorm_rope_qk: unsupported D=%d", D);
+  VC_RETURN_LAUNCH_STATUS("vc_rmsnorm_rope_qk");
+}
+
+int vc_patchify(const void* in, void* out, int C, int F, int H, int W, long long ld_out, void* stream) {
+  VC_CHECK_ARG(in && out && C > 0 && F > 0 && H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0, "vc_patchify: bad shape");
+  VC_CHECK_ARG(ld_out >= 4LL * C && ld_out % 4 == 0, "vc_patchify: bad ld_out");
+  long long total = (long long)F * (H / 2) * (W / 2) * C;
+  int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  patchify_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, C, F, H, W, ld_out);
+  VC_RETURN_LAUNCH_STATUS("vc_patchify");
+}
+
+int vc_unpatchify(const void* y, long long ldy, void* out, int Co, int gf, int gh, int gw, void* stream) {
+  VC_CHECK_ARG(y && out && Co > 0 && gf > 0 && gh > 0 && gw > 0 && ldy >= 4LL * Co, "vc_unpatchify: bad shape");
+  long long total = (long long)Co * gf * gh * gw * 4;
+  int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  unpatchify_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)out, Co, gf, gh, gw, ldy);
+  VC_RETURN_LAUNCH_STATUS("vc_unpatchify");
+}
+
+}  // extern "C"

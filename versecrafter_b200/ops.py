@@ -1,0 +1,206 @@
+"""Thin torch-tensor wrappers over the C ABI (include/vc_b200.h).  torch is used for device memory and the current
+stream only; every op below is one launch of a hand-written sm_100a kernel."""
+import ctypes
+import math
+
+import torch
+
+from . import _lib
+
+EPI_BIAS, EPI_GELU, EPI_GATE, EPI_RES, EPI_SCALE = 1, 2, 4, 8, 16
+
+# kernels launched through this module since the last reset (bench.py reports it as gpu_launches)
+launch_count = 0
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def _chk(t, name, dtype=torch.bfloat16):
+    if not t.is_cuda:
+        raise _lib.VCError(f"{name}: expected a CUDA tensor (the sm_100a path has no CPU fallback)")
+    if t.dtype != dtype:
+        raise _lib.VCError(f"{name}: expected {dtype}, got {t.dtype}")
+    if t.stride(-1) != 1:
+        raise _lib.VCError(f"{name}: innermost dimension must be contiguous")
+
+
+def _rows2d(t, name):
+    """View [..., D] as rows with one row stride; returns (rows, ld)."""
+    _chk(t, name)
+    if t.dim() == 2:
+        return t.shape[0], t.stride(0)
+    tt = t if t.is_contiguous() else None
+    if tt is None:
+        raise _lib.VCError(f"{name}: >2-D tensors must be contiguous")
+    return t.numel() // t.shape[-1], t.shape[-1]
+
+
+def ln_modulate(x, shift, scale, rows_per_batch, eps=1e-6, out=None):
+    """out = LN(x) * (1 + scale[b]) + shift[b];  x [rows, D] (or [B, L, D]); shift/scale [B, D] views (bf16)."""
+    global launch_count
+    rows, ldx = _rows2d(x, "x")
+    D = x.shape[-1]
+    _chk(shift, "shift"); _chk(scale, "scale")
+    assert shift.shape == scale.shape and shift.shape[-1] == D
+    sh2, sc2 = shift.reshape(-1, D) if shift.is_contiguous() else shift, scale.reshape(-1, D) if scale.is_contiguous() else scale
+    assert sh2.dim() == 2 and sc2.dim() == 2 and sh2.stride(0) == sc2.stride(0)
+    if out is None:
+        out = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+    _, ldo = _rows2d(out, "out")
+    lib = _lib.load()
+    _lib.check(lib.vc_ln_modulate(_ptr(x), ldx, _ptr(out), ldo, _ptr(sh2), _ptr(sc2), sh2.stride(0), rows,
+                                  rows_per_batch, D, eps, 0, _stream()), "vc_ln_modulate")
+    launch_count += 1
+    return out
+
+
+def ln_affine(x, gamma, beta, eps=1e-6, out=None):
+    """out = LN(x) * gamma + beta (norm3)."""
+    global launch_count
+    rows, ldx = _rows2d(x, "x")
+    D = x.shape[-1]
+    _chk(gamma, "gamma"); _chk(beta, "beta")
+    if out is None:
+        out = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+    _, ldo = _rows2d(out, "out")
+    lib = _lib.load()
+    _lib.check(lib.vc_ln_modulate(_ptr(x), ldx, _ptr(out), ldo, _ptr(beta), _ptr(gamma), 0, rows, max(rows, 1), D, eps, 1,
+                                  _stream()), "vc_ln_modulate")
+    launch_count += 1
+    return out
+
+
+def rope_table(head_dim, grid, device, theta=10000.0):
+    """(cos, sin) float2 tables per axis, fp64 angles rounded to fp32 (rope_params, wan_transformer3d.py:52-60 and the
+    table split at :783-795).  Returns (table [F*nf + H*nh + W*nw, 2] fp32, (nf, nh, nw))."""
+    c = head_dim // 2
+    nh = nw = c // 3
+    nf = c - 2 * (c // 3)
+    parts = []
+    for n_pos, n in zip(grid, (nf, nh, nw)):
+        dim = 2 * n
+        inv = 1.0 / torch.pow(torch.tensor(theta, dtype=torch.float64),
+                              torch.arange(0, dim, 2, dtype=torch.float64) / dim)
+        ang = torch.arange(n_pos, dtype=torch.float64)[:, None] * inv[None]
+        parts.append(torch.stack([ang.cos(), ang.sin()], dim=-1).reshape(-1, 2))
+    return torch.cat(parts).to(torch.float32).to(device).contiguous(), (nf, nh, nw)
+
+
+def rmsnorm_rope_(buf, D, n_mats, gain_q, gain_k, rows_per_batch, eps=1e-6, rope=None, grid=None, pos_offset=0):
+    """In place: first n_mats D-wide column blocks of buf [rows, ld] <- RoPE(RMSNorm(.) * gain).
+    rope = (table, (nf, nh, nw)) from rope_table, grid = (F, H', W'); rope=None -> RMSNorm only."""
+    global launch_count
+    _chk(buf, "buf")
+    assert buf.dim() == 2
+    rows, ld = buf.shape[0], buf.stride(0)
+    _chk(gain_q, "gain_q")
+    if gain_k is not None:
+        _chk(gain_k, "gain_k")
+    lib = _lib.load()
+    if rope is not None:
+        table, (nf, nh, nw) = rope
+        gf, gh, gw = grid
+        tptr, do = _ptr(table), 1
+    else:
+        nf = nh = nw = 0
+        gf = gh = gw = 1
+        tptr, do = ctypes.c_void_p(0), 0
+    _lib.check(lib.vc_rmsnorm_rope_qk(_ptr(buf), ld, rows, rows_per_batch, pos_offset, D, n_mats, _ptr(gain_q),
+                                      _ptr(gain_k), tptr, gf, gh, gw, nf, nh, nw, eps, do, _stream()),
+               "vc_rmsnorm_rope_qk")
+    launch_count += 1
+    return buf
+
+
+def gemm(a, w, bias=None, epilogue=None, gate=None, rows_per_batch=0, residual=None, scale=1.0, out=None):
+    """out[M,N] = epilogue(a[M,K] @ w[N,K]^T).  a / out / residual may be row-strided 2-D views."""
+    global launch_count
+    _chk(a, "a"); _chk(w, "w")
+    assert a.dim() == 2 and w.dim() == 2 and a.shape[1] == w.shape[1], (a.shape, w.shape)
+    M, K = a.shape
+    N = w.shape[0]
+    if epilogue is None:
+        epilogue = EPI_BIAS if bias is not None else 0
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    _chk(out, "out")
+    assert out.shape == (M, N)
+    gstride = 0
+    if gate is not None:
+        _chk(gate, "gate")
+        assert gate.dim() == 2 and gate.shape[1] == N
+        gstride = gate.stride(0)
+    ldr = 0
+    if residual is not None:
+        _chk(residual, "residual")
+        assert residual.shape == (M, N)
+        ldr = residual.stride(0)
+    if bias is not None:
+        _chk(bias, "bias")
+    lib = _lib.load()
+    _lib.check(lib.vc_gemm_bf16(_ptr(a), a.stride(0), _ptr(w), w.stride(0), _ptr(out), out.stride(0), M, N, K, epilogue,
+                                _ptr(bias), _ptr(gate), gstride, rows_per_batch, _ptr(residual), ldr, float(scale),
+                                _stream()), "vc_gemm_bf16")
+    launch_count += 1
+    return out
+
+
+def _strides3(t):
+    # t: [B, L, H, d] view
+    return (ctypes.c_longlong * 3)(t.stride(0), t.stride(1), t.stride(2))
+
+
+def flash_attn(q, k, v, out=None, softmax_scale=None, variant=0):
+    """q [B, Lq, H, 128], k/v [B, Lk, H, 128] (arbitrary batch/token/head strides, unit stride on head_dim)
+    -> out [B, Lq, H, 128]."""
+    global launch_count
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _chk(t, n)
+        assert t.dim() == 4 and t.shape[-1] == 128, (n, t.shape)
+    B, Lq, H, d = q.shape
+    Lk = k.shape[1]
+    assert k.shape == (B, Lk, H, d) and v.shape == (B, Lk, H, d)
+    if out is None:
+        out = torch.empty((B, Lq, H, d), dtype=torch.bfloat16, device=q.device)
+    _chk(out, "out")
+    if softmax_scale is None:
+        softmax_scale = 1.0 / math.sqrt(d)
+    lib = _lib.load()
+    _lib.check(lib.vc_flash_attn_fwd(_ptr(q), _ptr(k), _ptr(v), _ptr(out), B, H, Lq, Lk, d, _strides3(q), _strides3(k),
+                                     _strides3(v), _strides3(out), float(softmax_scale), int(variant), _stream()),
+               "vc_flash_attn_fwd")
+    launch_count += 1
+    return out
+
+
+def patchify(u, out=None):
+    """u [C, F, H, W] bf16 -> [L, 4C]."""
+    global launch_count
+    _chk(u, "u")
+    assert u.dim() == 4 and u.is_contiguous()
+    C, Fr, H, W = u.shape
+    L = Fr * (H // 2) * (W // 2)
+    if out is None:
+        out = torch.empty((L, 4 * C), dtype=torch.bfloat16, device=u.device)
+    lib = _lib.load()
+    _lib.check(lib.vc_patchify(_ptr(u), _ptr(out), C, Fr, H, W, out.stride(0), _stream()), "vc_patchify")
+    launch_count += 1
+    return out
+
+
+def unpatchify(y, grid, out_dim=16):
+    """y [L, 4*out_dim] -> [out_dim, F, 2H', 2W']."""
+    global launch_count
+    _chk(y, "y")
+    gf, gh, gw = grid
+    out = torch.empty((out_dim, gf, 2 * gh, 2 * gw), dtype=torch.bfloat16, device=y.device)
+    lib = _lib.load()
+    _lib.check(lib.vc_unpatchify(_ptr(y), y.stride(0), _ptr(out), out_dim, gf, gh, gw, _stream()), "vc_unpatchify")
+    launch_count += 1
+    return out
