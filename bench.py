@@ -1,0 +1,327 @@
+"""bench.py — one denoise-step forward of Wan2.1-14B + GeoAdapter (BASELINE.json metric), B200-native path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--config c3|c2|c1] [--impl b200|reference]
+  python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...      (N > 1: Ulysses sequence parallel)
+
+A "step" is one transformer forward (CFG batch 2, TeaCache off, cfg-skip off) on synthetic latents / control maps /
+text embeddings of the named shape with random non-trivial bf16 weights.  `value` times K steps with the inputs
+resident in HBM (CUDA events, max over ranks); `e2e` times the same K steps through the public forward() with the
+inputs in pinned host memory (H2D copies and the D2H read of the prediction inside the timed region).
+`--impl reference` times the oracle's CPU port of the reference path on the host cores (a bounded sample).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    # name: (ctor kwargs, latent (F, H, W), description)
+    "c3": (dict(dim=5120, ffn_dim=13824, num_heads=40, num_layers=40, text_dim=4096, geoada_in_dim=128),
+           (21, 60, 104), "Wan2.1-14B+GeoAdapter 81x480x832 (L=32760, CFG batch 2)"),
+    "c4": (dict(dim=5120, ffn_dim=13824, num_heads=40, num_layers=40, text_dim=4096, geoada_in_dim=128),
+           (21, 90, 160), "Wan2.1-14B+GeoAdapter 81x720x1280 (L=75600, CFG batch 2)"),
+    "c2": (dict(dim=1536, ffn_dim=8960, num_heads=12, num_layers=30, text_dim=4096, geoada_in_dim=128),
+           (21, 60, 104), "Wan2.1-1.3B-arch+GeoAdapter 81x480x832 (L=32760, CFG batch 2)"),
+    "c1": (dict(dim=512, ffn_dim=2048, num_heads=4, num_layers=2, text_dim=4096, geoada_in_dim=128),
+           (5, 30, 52), "reduced-depth DiT (2 blocks, dim 512)+GeoAdapter 5x30x52 (L=1950, CFG batch 2)"),
+}
+
+
+def load_peaks():
+    p = dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, source="fallback")
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p.update(json.load(f))
+        p["source"] = "measured"
+    except Exception:  # noqa: BLE001
+        pass
+    return p
+
+
+def work_per_step(cfg, L, B, T=512):
+    """Algorithmic FLOPs of one step."""
+    D, Fd, nb = cfg["dim"], cfg["ffn_dim"], cfg["num_layers"]
+    ng = len(cfg.get("geoada_layers") or range(0, nb, 2))
+    gemm_blk = 8 * L * D * D + 4 * L * D * D + 4 * T * D * D + 4 * L * D * Fd
+    attn_blk = 4 * L * L * D + 4 * L * T * D
+    gemm = B * ((nb + ng) * gemm_blk + ng * 2 * L * D * D + 2 * L * D * D + 2 * L * D * (64 + 512 + 64))
+    attn = B * (nb + ng) * attn_blk
+    return float(gemm), float(attn)
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "200"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+            except Exception:  # noqa: BLE001
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_inputs(cfg, grid, B=2):
+    """Synthetic inputs in pinned host memory, bf16."""
+    g = torch.Generator().manual_seed(77)
+    Fr, Hh, Ww = grid
+    x = torch.randn(B, cfg.get("in_dim", 16), Fr, Hh, Ww, generator=g).to(torch.bfloat16)
+    half = cfg["geoada_in_dim"] // 2
+    ctrl = torch.cat([torch.randn(half, Fr, Hh, Ww, generator=g),
+                      (torch.rand(cfg["geoada_in_dim"] - half, Fr, Hh, Ww, generator=g) > 0.5).float()]).to(torch.bfloat16)
+    geo = torch.stack([ctrl] * B)
+    ctx = [(0.1 * torch.randn(n, cfg["text_dim"], generator=g)).to(torch.bfloat16) for n in ([37, 512] * B)[:B]]
+    t = torch.full((B,), 500.0)
+    pin = lambda u: u.pin_memory() if torch.cuda.is_available() else u
+    return dict(x=pin(x), geo=pin(geo), ctx=[pin(c) for c in ctx], t=pin(t), seq_len=Fr * (Hh // 2) * (Ww // 2))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle's port of the reference path, timed on the host cores on a bounded sample
+# ------------------------------------------------------------------------------------------------------------------
+def cpu_reference_sample(cfg_name, steps=1, warmup=0, seconds_budget=25.0):
+    """One DiT block (the reference's WanAttentionBlock.forward restated in oracle/restate.py) at the config's real
+    width, fp32, on a token sample sized to the time budget; tokens/s is extrapolated to a full step by the block count
+    (optimistic for the CPU: attention is quadratic in L and the sample is short)."""
+    from oracle import restate
+    cfg, grid, _ = CONFIGS[cfg_name]
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    D, H = cfg["dim"], cfg["num_heads"]
+    sgrid = (2, 16, 32) if D >= 1536 else (5, 15, 26)   # 1024 / 1950 tokens
+    Ls = sgrid[0] * sgrid[1] * sgrid[2]
+    one = dict(cfg, num_layers=1)
+    shapes = restate.block_param_shapes(D, cfg["ffn_dim"])
+    g = torch.Generator().manual_seed(0)
+    sd = {"b." + k: (torch.randn(s, generator=g) * (0.02 if len(s) > 1 else 0.1) + (1.0 if "norm" in k and k.endswith("weight") else 0.0))
+          for k, s in shapes.items()}
+    x = torch.randn(1, Ls, D, generator=g)
+    e0 = torch.randn(1, 6, D, generator=g) * 0.1
+    ctx = torch.randn(1, 512, D, generator=g)
+    ang = restate.rope_angles(D // H, sgrid)
+    times = []
+    with torch.no_grad():
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            restate.dit_block(sd, "b.", x, e0, ang, ctx, H)
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                times.append(dt)
+            if sum(times) > seconds_budget and times:
+                break
+    n_blocks = cfg["num_layers"] + len(range(0, cfg["num_layers"], 2))
+    t_blk = sum(times) / len(times)
+    tokens_per_s = Ls / (t_blk * n_blocks)
+    return dict(value=tokens_per_s, unit="tokens/s", cores=cores, kind="port",
+                sample=f"oracle/restate.dit_block fp32, 1 block of {n_blocks} at dim {D}, batch 1, {Ls} tokens "
+                       f"({sgrid}), {len(times)} run(s), {t_blk:.2f} s/block; tokens/s = {Ls}/(s_per_block*{n_blocks}) "
+                       f"[extrapolated to a full step; attention cost at the real L is ~{(CONFIGS[cfg_name][1][0]*CONFIGS[cfg_name][1][1]*CONFIGS[cfg_name][1][2]//4)//Ls}x larger per token]"), t_blk
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb, t_blk = cpu_reference_sample(args.config, steps=max(1, args.steps), warmup=min(args.warmup, 1))
+    cfg, grid, desc = CONFIGS[args.config]
+    line = {"impl": "reference", "metric": "video_tokens_per_s", "value": cb["value"], "unit": "tokens/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_blk * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "note": "CPU port of the reference path on a bounded sample; ms_per_step is one block of the sample"},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------------------------
+def summarize_timing(timing, peaks):
+    """Per kernel class: launches, mean device ms per launch, achieved TFLOP/s or GB/s (work = algorithmic flops/bytes)."""
+    out = {}
+    for name, recs in timing.items():
+        ms = [a.elapsed_time(b) for a, b, _ in recs]
+        work = sum(w for _, _, w in recs)
+        tot = sum(ms)
+        if tot <= 0:
+            continue
+        ent = {"launches": len(recs), "ms_total": tot, "ms_per_launch": tot / len(recs)}
+        if name in ("gemm", "attn_self", "attn_cross"):
+            ent["tflops"] = work / tot / 1e9
+            ent["frac_of_bf16_sustained"] = ent["tflops"] / peaks["bf16_tflops_sustained"]
+        else:
+            ent["gbs"] = work / tot / 1e6
+            ent["frac_of_hbm"] = ent["gbs"] / peaks["hbm_gbs"]
+        out[name] = ent
+    return out
+
+
+def run_gpu_arm(args):
+    import torch.distributed as dist
+    from versecrafter_b200 import _lib, ops
+    from versecrafter_b200.transformer import VerseCrafterWanTransformer3DModel
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    lib = _lib.load()
+    _lib.check(lib.vc_device_ok(), "vc_device_ok")
+    peaks = load_peaks()
+    cfg, grid, desc = CONFIGS[args.config]
+    B = 2
+    L = grid[0] * (grid[1] // 2) * (grid[2] // 2)
+
+    model = VerseCrafterWanTransformer3DModel(**cfg, device="cuda", dtype=torch.bfloat16, init=False)
+    model.synthetic_init_(seed=0)
+    model.eval()
+    if world > 1:
+        model.enable_multi_gpus_inference()
+    host = make_inputs(cfg, grid, B)
+    dev = dict(x=host["x"].cuda(), geo=host["geo"].cuda(), ctx=[c.cuda() for c in host["ctx"]], t=host["t"].cuda())
+
+    def step_resident():
+        return model(x=dev["x"], t=dev["t"], geoada_context=dev["geo"], context=dev["ctx"], seq_len=host["seq_len"],
+                     geoada_context_scale=1.0)
+
+    def step_e2e():
+        x = host["x"].cuda(non_blocking=True)
+        geo = host["geo"].cuda(non_blocking=True)
+        ctx = [c.cuda(non_blocking=True) for c in host["ctx"]]
+        t = host["t"].cuda(non_blocking=True)
+        y = model(x=x, t=t, geoada_context=geo, context=ctx, seq_len=host["seq_len"], geoada_context_scale=1.0)
+        return y.cpu()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), out
+
+    for _ in range(args.warmup):
+        y = step_resident()
+    torch.cuda.synchronize()
+    assert torch.isfinite(y.float()).all(), "non-finite prediction"
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ops.launch_count = 0
+    ops.timing = {}
+    ms_total, y = timed(step_resident, args.steps)
+    launches = ops.launch_count
+    timing, ops.timing = ops.timing, None
+    clocks = sampler.stop() if rank == 0 else None
+    # end to end through the public forward() with host buffers
+    step_e2e()
+    ms_e2e, y_host = timed(step_e2e, args.steps)
+
+    ms_step = ms_total / args.steps
+    tokens = B * L
+    value = tokens / (ms_step / 1e3)
+    h2d = host["x"].numel() * 2 + host["geo"].numel() * 2 + sum(c.numel() * 2 for c in host["ctx"]) + host["t"].numel() * 4
+    d2h = y_host.numel() * y_host.element_size()
+    kern = summarize_timing(timing, peaks)
+    gemm_f, attn_f = work_per_step(cfg, L, B)
+    dom = kern.get("attn_self", {})
+    # dominant kernel: self-attention (52 % of the step's FLOPs at c3); algorithmic flops per launch = 4*B*(H/P)*L^2*128
+    flops_launch = 4.0 * B * (cfg["num_heads"] / world) * L * L * 128
+    achieved = flops_launch / (dom.get("ms_per_launch", float("inf")) * 1e9) if dom else None
+    roofline = {"kernel": "flash_attn_kernel (self-attention)", "bound": "tensor", "achieved": achieved,
+                "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                "frac": achieved / peaks["bf16_tflops_sustained"] if achieved else None,
+                "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['source']}); kernel timed inside a long step",
+                "traffic": None, "flops_per_launch": flops_launch, "ms_per_launch": dom.get("ms_per_launch")}
+    line = {"metric": "video_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "s_per_denoise_step": ms_step / 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": desc, "name": args.config, "tokens_per_step": tokens, "batch": B, "seq_len": L,
+                       "parallelism": f"ulysses_sp{world}", "l2": "working set per kernel >> 126 MB L2 (no flush needed)",
+                       "teacache": "off", "cfg_skip": "off", "weights": "random non-trivial bf16 (synthetic_init_)"},
+            "step_pflop": (gemm_f + attn_f) / 1e15,
+            "step_frac_of_bf16_sustained": (gemm_f + attn_f) / world / (ms_step * 1e9) / peaks["bf16_tflops_sustained"],
+            "roofline": roofline, "kernels": kern, "clocks": clocks,
+            "e2e": {"value": tokens / (ms_e2e / args.steps / 1e3), "unit": "tokens/s", "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": launches}
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                line["cpu_baseline"], _ = cpu_reference_sample(args.config, steps=1, warmup=0)
+            except Exception as e:  # noqa: BLE001
+                line["cpu_baseline"] = {"error": repr(e)[:200]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--config", default=os.environ.get("VC_BENCH_CONFIG", "c3"), choices=sorted(CONFIGS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -12,6 +12,28 @@ EPI_BIAS, EPI_GELU, EPI_GATE, EPI_RES, EPI_SCALE = 1, 2, 4, 8, 16
 # kernels launched through this module since the last reset (bench.py reports it as gpu_launches)
 launch_count = 0
 
+# optional per-kernel-class device timing: bench.py sets `timing = {}`; every wrapper then brackets its launch with
+# CUDA events on the current stream and appends (start, end, work) under its class name.
+timing = None
+
+
+class _timed:
+    def __init__(self, name, work=0.0):
+        self.name, self.work = name, work
+
+    def __enter__(self):
+        if timing is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *a):
+        if timing is not None:
+            self.e1.record()
+            timing.setdefault(self.name, []).append((self.e0, self.e1, self.work))
+        return False
+
 
 def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
@@ -54,8 +76,9 @@ def ln_modulate(x, shift, scale, rows_per_batch, eps=1e-6, out=None):
         out = torch.empty(x.shape, dtype=x.dtype, device=x.device)
     _, ldo = _rows2d(out, "out")
     lib = _lib.load()
-    _lib.check(lib.vc_ln_modulate(_ptr(x), ldx, _ptr(out), ldo, _ptr(sh2), _ptr(sc2), sh2.stride(0), rows,
-                                  rows_per_batch, D, eps, 0, _stream()), "vc_ln_modulate")
+    with _timed("ln_modulate", 4.0 * rows * D):
+        _lib.check(lib.vc_ln_modulate(_ptr(x), ldx, _ptr(out), ldo, _ptr(sh2), _ptr(sc2), sh2.stride(0), rows,
+                                      rows_per_batch, D, eps, 0, _stream()), "vc_ln_modulate")
     launch_count += 1
     return out
 
@@ -70,8 +93,9 @@ def ln_affine(x, gamma, beta, eps=1e-6, out=None):
         out = torch.empty(x.shape, dtype=x.dtype, device=x.device)
     _, ldo = _rows2d(out, "out")
     lib = _lib.load()
-    _lib.check(lib.vc_ln_modulate(_ptr(x), ldx, _ptr(out), ldo, _ptr(beta), _ptr(gamma), 0, rows, max(rows, 1), D, eps, 1,
-                                  _stream()), "vc_ln_modulate")
+    with _timed("ln_affine", 4.0 * rows * D):
+        _lib.check(lib.vc_ln_modulate(_ptr(x), ldx, _ptr(out), ldo, _ptr(beta), _ptr(gamma), 0, rows, max(rows, 1), D, eps,
+                                      1, _stream()), "vc_ln_modulate")
     launch_count += 1
     return out
 
@@ -111,9 +135,10 @@ def rmsnorm_rope_(buf, D, n_mats, gain_q, gain_k, rows_per_batch, eps=1e-6, rope
         nf = nh = nw = 0
         gf = gh = gw = 1
         tptr, do = ctypes.c_void_p(0), 0
-    _lib.check(lib.vc_rmsnorm_rope_qk(_ptr(buf), ld, rows, rows_per_batch, pos_offset, D, n_mats, _ptr(gain_q),
-                                      _ptr(gain_k), tptr, gf, gh, gw, nf, nh, nw, eps, do, _stream()),
-               "vc_rmsnorm_rope_qk")
+    with _timed("rmsnorm_rope", 4.0 * rows * D * n_mats):
+        _lib.check(lib.vc_rmsnorm_rope_qk(_ptr(buf), ld, rows, rows_per_batch, pos_offset, D, n_mats, _ptr(gain_q),
+                                          _ptr(gain_k), tptr, gf, gh, gw, nf, nh, nw, eps, do, _stream()),
+                   "vc_rmsnorm_rope_qk")
     launch_count += 1
     return buf
 
@@ -144,9 +169,10 @@ def gemm(a, w, bias=None, epilogue=None, gate=None, rows_per_batch=0, residual=N
     if bias is not None:
         _chk(bias, "bias")
     lib = _lib.load()
-    _lib.check(lib.vc_gemm_bf16(_ptr(a), a.stride(0), _ptr(w), w.stride(0), _ptr(out), out.stride(0), M, N, K, epilogue,
-                                _ptr(bias), _ptr(gate), gstride, rows_per_batch, _ptr(residual), ldr, float(scale),
-                                _stream()), "vc_gemm_bf16")
+    with _timed("gemm", 2.0 * M * N * K):
+        _lib.check(lib.vc_gemm_bf16(_ptr(a), a.stride(0), _ptr(w), w.stride(0), _ptr(out), out.stride(0), M, N, K,
+                                    epilogue, _ptr(bias), _ptr(gate), gstride, rows_per_batch, _ptr(residual), ldr,
+                                    float(scale), _stream()), "vc_gemm_bf16")
     launch_count += 1
     return out
 
@@ -172,9 +198,10 @@ def flash_attn(q, k, v, out=None, softmax_scale=None, variant=0):
     if softmax_scale is None:
         softmax_scale = 1.0 / math.sqrt(d)
     lib = _lib.load()
-    _lib.check(lib.vc_flash_attn_fwd(_ptr(q), _ptr(k), _ptr(v), _ptr(out), B, H, Lq, Lk, d, _strides3(q), _strides3(k),
-                                     _strides3(v), _strides3(out), float(softmax_scale), int(variant), _stream()),
-               "vc_flash_attn_fwd")
+    with _timed("attn_self" if Lk > 1024 else "attn_cross", 4.0 * B * H * Lq * Lk * d):
+        _lib.check(lib.vc_flash_attn_fwd(_ptr(q), _ptr(k), _ptr(v), _ptr(out), B, H, Lq, Lk, d, _strides3(q),
+                                         _strides3(k), _strides3(v), _strides3(out), float(softmax_scale), int(variant),
+                                         _stream()), "vc_flash_attn_fwd")
     launch_count += 1
     return out
 

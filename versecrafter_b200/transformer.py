@@ -1,0 +1,636 @@
+"""Drop-in for the reference's `VerseCrafterWanTransformer3DModel`
+(/root/reference/versecrafter/models/wan_transformer3d_versecrafter.py:151-442 on top of wan_transformer3d.py:663-1322):
+same constructor kwargs, state-dict keys, forward signature and caller-visible attributes, with the
+denoise-step arithmetic executed by the hand-written sm_100a kernels of libvc_b200.so (include/vc_b200.h).
+
+What is different from the reference by design (results identical within the bf16 tolerance):
+  * q/k/v (and cross k/v) Linears run as ONE fused-N GEMM; their parameters are views into the packed weight, so the
+    state dict keeps the reference's keys and load_state_dict() writes straight into the packed storage.
+  * GeoAdapter block j runs right before the backbone layer that consumes its hint and `after_proj` accumulates
+    `x += scale * hint` in its GEMM epilogue: no hint tensors, no torch.stack copies.
+  * LayerNorm+modulate, RMSNorm+RoPE, bias/GELU/gate/residual are fused into single kernels.
+There is no PyTorch/CPU fallback: without the CUDA library forward() raises.
+"""
+import glob
+import json
+import math
+import os
+from types import SimpleNamespace
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import ops, sp
+from ._lib import VCError
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# parameter holders (names mirror the reference modules so the state-dict keys are identical)
+# ------------------------------------------------------------------------------------------------------------------
+class _Linear(nn.Module):
+    def __init__(self, in_f, out_f, **fk):
+        super().__init__()
+        self.in_features, self.out_features = in_f, out_f
+        self.weight = nn.Parameter(torch.empty(out_f, in_f, **fk), requires_grad=False)
+        self.bias = nn.Parameter(torch.empty(out_f, **fk), requires_grad=False)
+
+
+class _Gain(nn.Module):
+    def __init__(self, dim, **fk):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(dim, **fk), requires_grad=False)
+
+
+class _Affine(nn.Module):
+    def __init__(self, dim, **fk):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(dim, **fk), requires_grad=False)
+        self.bias = nn.Parameter(torch.zeros(dim, **fk), requires_grad=False)
+
+
+class _Conv3dHolder(nn.Module):
+    def __init__(self, in_c, out_c, patch, **fk):
+        super().__init__()
+        self.weight = nn.Parameter(torch.empty(out_c, in_c, *patch, **fk), requires_grad=False)
+        self.bias = nn.Parameter(torch.empty(out_c, **fk), requires_grad=False)
+
+
+class WanSelfAttention(nn.Module):
+    """Holder for q/k/v/o + norm_q/norm_k (wan_transformer3d.py:348-371)."""
+
+    def __init__(self, dim, num_heads, **fk):
+        super().__init__()
+        self.dim, self.num_heads, self.head_dim = dim, num_heads, dim // num_heads
+        self.q, self.k, self.v, self.o = (_Linear(dim, dim, **fk) for _ in range(4))
+        self.norm_q, self.norm_k = _Gain(dim, **fk), _Gain(dim, **fk)
+
+
+class WanAttentionBlock(nn.Module):
+    """Parameter holder for one DiT block (wan_transformer3d.py:524-562); `block_id` as in
+    BaseWanAttentionBlock / VerseCrafterWanAttentionBlock (wan_transformer3d_versecrafter.py:89-148)."""
+
+    def __init__(self, dim, ffn_dim, num_heads, block_id=None, geo=False, **fk):
+        super().__init__()
+        self.dim, self.ffn_dim, self.num_heads, self.block_id = dim, ffn_dim, num_heads, block_id
+        self.self_attn = WanSelfAttention(dim, num_heads, **fk)
+        self.norm3 = _Affine(dim, **fk)
+        self.cross_attn = WanSelfAttention(dim, num_heads, **fk)
+        self.ffn = nn.Sequential(_Linear(dim, ffn_dim, **fk), nn.Identity(), _Linear(ffn_dim, dim, **fk))
+        self.modulation = nn.Parameter(torch.empty(1, 6, dim, **fk), requires_grad=False)
+        if geo:
+            if block_id == 0:
+                self.before_proj = _Linear(dim, dim, **fk)
+            self.after_proj = _Linear(dim, dim, **fk)
+        self._packed = None
+
+    # -- packed weights: one [3D, D] buffer for self q|k|v and one [2D, D] for cross k|v; params become views -----
+    def ensure_packed(self):
+        sa, ca = self.self_attn, self.cross_attn
+        pk = self._packed
+        if pk is not None and sa.q.weight.data_ptr() == pk["wqkv"].data_ptr() \
+                and ca.k.weight.data_ptr() == pk["wkv"].data_ptr() and pk["wqkv"].device == sa.q.weight.device:
+            return pk
+        D = self.dim
+
+        def fuse(mods):
+            w = torch.cat([m.weight.data for m in mods], dim=0)
+            b = torch.cat([m.bias.data for m in mods], dim=0)
+            for i, m in enumerate(mods):
+                m.weight.data = w[i * D:(i + 1) * D]
+                m.bias.data = b[i * D:(i + 1) * D]
+            return w, b
+
+        wqkv, bqkv = fuse([sa.q, sa.k, sa.v])
+        wkv, bkv = fuse([ca.k, ca.v])
+        self._packed = dict(wqkv=wqkv, bqkv=bqkv, wkv=wkv, bkv=bkv)
+        return self._packed
+
+
+BaseWanAttentionBlock = WanAttentionBlock
+VerseCrafterWanAttentionBlock = WanAttentionBlock
+
+
+class Head(nn.Module):
+    def __init__(self, dim, out_dim, patch_size, **fk):
+        super().__init__()
+        self.head = _Linear(dim, math.prod(patch_size) * out_dim, **fk)
+        self.modulation = nn.Parameter(torch.empty(1, 2, dim, **fk), requires_grad=False)
+
+
+class TeaCache:
+    """Step-skipping cache with the attribute surface the reference touches (wan_transformer3d.py:205-245,
+    :828-843): rel-L1 drift of the modulation input, rescaled by a polynomial, accumulated until
+    it crosses `rel_l1_thresh`."""
+
+    def __init__(self, coefficients, num_steps, rel_l1_thresh, num_skip_start_steps=0, offload=True):
+        self.coefficients, self.num_steps, self.rel_l1_thresh = coefficients, num_steps, rel_l1_thresh
+        self.num_skip_start_steps, self.offload = num_skip_start_steps, offload
+        self.rescale_func = np.poly1d(coefficients)
+        self.reset()
+
+    @staticmethod
+    def compute_rel_l1_distance(prev, cur):
+        return ((prev.float() - cur.float()).abs().mean() / prev.float().abs().mean()).cpu().item()
+
+    def reset(self):
+        self.cnt = 0
+        self.should_calc = True
+        self.accumulated_rel_l1_distance = 0
+        self.previous_modulated_input = None
+        self.previous_residual = None
+        self.previous_residual_cond = None
+        self.previous_residual_uncond = None
+
+
+def rope_params(max_seq_len, dim, theta=10000.0, k=None, L_test=None, L_test_scale=None):
+    """complex128 [max_seq_len, dim/2] table (wan_transformer3d.py:52-60); with k/L_test the RIFLEx change of the
+    k-th frequency (:62-118)."""
+    freqs = 1.0 / torch.pow(theta, torch.arange(0, dim, 2, dtype=torch.float64) / dim)
+    if k is not None:
+        freqs[k - 1] = 0.9 * 2 * math.pi / L_test
+        if L_test_scale is not None:
+            freqs[k - 1] = freqs[k - 1] / L_test_scale
+    ang = torch.outer(torch.arange(max_seq_len, dtype=torch.float64), freqs)
+    return torch.polar(torch.ones_like(ang), ang)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+class VerseCrafterWanTransformer3DModel(nn.Module):
+    """See module docstring.  Extra (optional) ctor kwargs beyond the reference's: `device`, `dtype`
+    (allocate parameters directly there, e.g. 14B straight on the GPU) and `init` (False = leave them uninitialised
+    for a following load_state_dict)."""
+
+    def __init__(self, geoada_layers=None, geoada_in_dim=None, model_type="t2v", patch_size=(1, 2, 2), text_len=512,
+                 in_dim=16, dim=2048, ffn_dim=8192, freq_dim=256, text_dim=4096, out_dim=16, num_heads=16,
+                 num_layers=32, window_size=(-1, -1), qk_norm=True, cross_attn_norm=True, eps=1e-6,
+                 device=None, dtype=None, init=True):
+        super().__init__()
+        if tuple(patch_size) != (1, 2, 2):
+            raise VCError("only patch_size (1,2,2) is implemented (the Wan2.1 value)")
+        if dim % num_heads or dim // num_heads != 128:
+            raise VCError(f"head_dim must be 128 for the tcgen05 attention kernel (dim={dim}, heads={num_heads})")
+        if not (qk_norm and cross_attn_norm) or tuple(window_size) != (-1, -1):
+            raise VCError("qk_norm=True, cross_attn_norm=True, window_size=(-1,-1) are the only supported settings")
+        self.model_type = "t2v"  # hard-coded by the reference (wan_transformer3d_versecrafter.py:171)
+        self.patch_size, self.text_len, self.in_dim, self.dim, self.ffn_dim = tuple(patch_size), text_len, in_dim, dim, ffn_dim
+        self.freq_dim, self.text_dim, self.out_dim, self.num_heads, self.num_layers = freq_dim, text_dim, out_dim, num_heads, num_layers
+        self.window_size, self.qk_norm, self.cross_attn_norm, self.eps = window_size, qk_norm, cross_attn_norm, eps
+        self.geoada_layers = list(range(0, num_layers, 2)) if geoada_layers is None else list(geoada_layers)
+        self.geoada_in_dim = in_dim if geoada_in_dim is None else geoada_in_dim
+        assert 0 in self.geoada_layers
+        self.geoada_layers_mapping = {i: n for n, i in enumerate(self.geoada_layers)}
+        self.config = SimpleNamespace(
+            geoada_layers=geoada_layers, geoada_in_dim=geoada_in_dim, model_type="t2v", patch_size=tuple(patch_size),
+            text_len=text_len, in_dim=in_dim, dim=dim, ffn_dim=ffn_dim, freq_dim=freq_dim, text_dim=text_dim,
+            out_dim=out_dim, num_heads=num_heads, num_layers=num_layers, window_size=window_size, qk_norm=qk_norm,
+            cross_attn_norm=cross_attn_norm, eps=eps)
+        fk = dict(device=device, dtype=dtype)
+
+        self.patch_embedding = _Conv3dHolder(in_dim, dim, self.patch_size, **fk)
+        self.text_embedding = nn.Sequential(_Linear(text_dim, dim, **fk), nn.Identity(), _Linear(dim, dim, **fk))
+        self.time_embedding = nn.Sequential(_Linear(freq_dim, dim, **fk), nn.Identity(), _Linear(dim, dim, **fk))
+        self.time_projection = nn.Sequential(nn.Identity(), _Linear(dim, dim * 6, **fk))
+        self.blocks = nn.ModuleList([
+            WanAttentionBlock(dim, ffn_dim, num_heads, block_id=self.geoada_layers_mapping.get(i), **fk)
+            for i in range(num_layers)])
+        self.geoada_blocks = nn.ModuleList([
+            WanAttentionBlock(dim, ffn_dim, num_heads, block_id=i, geo=True, **fk) for i in self.geoada_layers])
+        self.head = Head(dim, out_dim, self.patch_size, **fk)
+        self.geoada_patch_embedding = _Conv3dHolder(self.geoada_in_dim, dim, self.patch_size, **fk)
+
+        self.d = dim // num_heads
+        self.freqs = torch.cat([rope_params(1024, self.d - 4 * (self.d // 6)), rope_params(1024, 2 * (self.d // 6)),
+                                rope_params(1024, 2 * (self.d // 6))], dim=1)
+        self.teacache = None
+        self.cfg_skip_ratio = None
+        self.current_steps = 0
+        self.num_inference_steps = None
+        self.gradient_checkpointing = False
+        self.sp_world_size, self.sp_world_rank, self.sp_group = 1, 0, None
+        self.attn_variant = int(os.environ.get("VC_ATTN_VARIANT", "1"))
+        self._ws = {}
+        self._rope_cache = {}
+        self.record = None  # optional dict: tests set it to capture per-block tensors
+        if init:
+            self.init_weights()
+
+    # -- reference-compatible initialisation (wan_transformer3d.py:1152-1174 + block defaults) ----
+    @torch.no_grad()
+    def init_weights(self):
+        def default_linear(m):
+            bound = 1.0 / math.sqrt(m.weight.shape[1])
+            m.weight.uniform_(-bound, bound)
+            m.bias.uniform_(-bound, bound)
+
+        for m in list(self.blocks.modules()) + list(self.geoada_blocks.modules()):
+            if isinstance(m, _Linear):
+                default_linear(m)
+            if isinstance(m, WanAttentionBlock):
+                m.modulation.normal_().div_(math.sqrt(self.dim))
+        for blk in self.geoada_blocks:  # zero-initialised adapter projections (:104-110)
+            for name in ("before_proj", "after_proj"):
+                if hasattr(blk, name):
+                    getattr(blk, name).weight.zero_()
+                    getattr(blk, name).bias.zero_()
+        for seq, std in ((self.text_embedding, 0.02), (self.time_embedding, 0.02)):
+            for m in seq:
+                if isinstance(m, _Linear):
+                    m.weight.normal_(std=std)
+                    m.bias.zero_()
+        lin = self.time_projection[1]
+        nn.init.xavier_uniform_(lin.weight)
+        lin.bias.zero_()
+        for conv in (self.patch_embedding, self.geoada_patch_embedding):
+            nn.init.xavier_uniform_(conv.weight.flatten(1))
+            bound = 1.0 / math.sqrt(conv.weight[0].numel())
+            conv.bias.uniform_(-bound, bound)
+        self.head.head.weight.zero_()
+        self.head.head.bias.zero_()
+        self.head.modulation.normal_().div_(math.sqrt(self.dim))
+
+    @torch.no_grad()
+    def synthetic_init_(self, seed=0):
+        """Random NON-TRIVIAL weights generated in place on the parameters' device (benchmarks: there are no
+        checkpoints offline).  Unlike init_weights() nothing stays at 0 or 1: Linear/conv weights U(-1/sqrt(fan_in),
+        +1/sqrt(fan_in)), biases N(0, 0.02^2), RMSNorm/LayerNorm gains 1 + N(0, 0.1^2), modulation N(0,1)/sqrt(D)."""
+        g = torch.Generator(device=self.device).manual_seed(seed)
+        for name, p in self.named_parameters():
+            if name.endswith("modulation"):
+                p.copy_(torch.randn(p.shape, generator=g, device=p.device, dtype=torch.float32) / math.sqrt(self.dim))
+            elif name.endswith(("norm_q.weight", "norm_k.weight", "norm3.weight")):
+                p.copy_(1.0 + 0.1 * torch.randn(p.shape, generator=g, device=p.device, dtype=torch.float32))
+            elif name.endswith("bias"):
+                p.copy_(0.02 * torch.randn(p.shape, generator=g, device=p.device, dtype=torch.float32))
+            else:
+                bound = 1.0 / math.sqrt(p[0].numel())
+                p.uniform_(-bound, bound, generator=g)
+        return self
+
+    @property
+    def dtype(self):
+        return self.patch_embedding.weight.dtype
+
+    @property
+    def device(self):
+        return self.patch_embedding.weight.device
+
+    # -- caller-visible switches (wan_transformer3d.py:828-921) ------------------------------------------------------
+    def enable_teacache(self, coefficients, num_steps, rel_l1_thresh, num_skip_start_steps=0, offload=True):
+        self.teacache = TeaCache(coefficients, num_steps, rel_l1_thresh=rel_l1_thresh,
+                                 num_skip_start_steps=num_skip_start_steps, offload=offload)
+
+    def share_teacache(self, transformer=None):
+        self.teacache = transformer.teacache
+
+    def disable_teacache(self):
+        self.teacache = None
+
+    def enable_cfg_skip(self, cfg_skip_ratio, num_steps):
+        if cfg_skip_ratio != 0:
+            self.cfg_skip_ratio, self.current_steps, self.num_inference_steps = cfg_skip_ratio, 0, num_steps
+        else:
+            self.disable_cfg_skip()
+
+    def share_cfg_skip(self, transformer=None):
+        self.cfg_skip_ratio = transformer.cfg_skip_ratio
+        self.current_steps = transformer.current_steps
+        self.num_inference_steps = transformer.num_inference_steps
+
+    def disable_cfg_skip(self):
+        self.cfg_skip_ratio, self.current_steps, self.num_inference_steps = None, 0, None
+
+    def enable_riflex(self, k=6, L_test=66, L_test_scale=4.886):
+        dev = self.freqs.device
+        self.freqs = torch.cat([rope_params(1024, self.d - 4 * (self.d // 6), k=k, L_test=L_test, L_test_scale=L_test_scale),
+                                rope_params(1024, 2 * (self.d // 6)), rope_params(1024, 2 * (self.d // 6))], dim=1).to(dev)
+        self._rope_cache.clear()
+
+    def disable_riflex(self):
+        dev = self.freqs.device
+        self.freqs = torch.cat([rope_params(1024, self.d - 4 * (self.d // 6)), rope_params(1024, 2 * (self.d // 6)),
+                                rope_params(1024, 2 * (self.d // 6))], dim=1).to(dev)
+        self._rope_cache.clear()
+
+    def enable_multi_gpus_inference(self, group=None):
+        """Ulysses sequence parallelism over the given (default: world) process group — the reference binds
+        xfuser's Ulysses x ring group here (wan_transformer3d.py:901-921); ring is dropped by design."""
+        import torch.distributed as dist
+        self.sp_group = group
+        self.sp_world_size = dist.get_world_size(group)
+        self.sp_world_rank = dist.get_rank(group)
+        if self.num_heads % self.sp_world_size:
+            raise VCError(f"{self.num_heads} heads do not split over {self.sp_world_size} ranks")
+
+    def all_gather(self, x, dim=1):
+        return sp.all_gather_tokens(x, dim, self.sp_group)
+
+    # -- loading (wan_transformer3d.py:1176-1322, wan_transformer3d_versecrafter.py:203-252) --------------------------
+    @classmethod
+    def from_config(cls, config, **kw):
+        import inspect
+        sig = inspect.signature(cls.__init__).parameters
+        return cls(**{k: v for k, v in dict(config, **kw).items() if k in sig})
+
+    @classmethod
+    def from_pretrained(cls, pretrained_model_path, subfolder=None, transformer_additional_kwargs={},
+                        low_cpu_mem_usage=False, torch_dtype=torch.bfloat16):
+        if subfolder is not None:
+            pretrained_model_path = os.path.join(pretrained_model_path, subfolder)
+        config_file = os.path.join(pretrained_model_path, "config.json")
+        if not os.path.isfile(config_file):
+            raise RuntimeError(f"{config_file} does not exist")
+        with open(config_file) as f:
+            config = json.load(f)
+        kw = dict(transformer_additional_kwargs)
+        for key, dst in kw.pop("dict_mapping", {}).items():
+            kw[dst] = config[key]
+        geo_changed = kw.get("geoada_in_dim", config.get("geoada_in_dim", config.get("in_dim", 16))) != \
+            config.get("geoada_in_dim", config.get("in_dim", 16))
+        model = cls.from_config(config, dtype=torch_dtype, **kw)
+        state = {}
+        bin_file = os.path.join(pretrained_model_path, "diffusion_pytorch_model.bin")
+        st_file = bin_file.replace(".bin", ".safetensors")
+        if os.path.exists(bin_file):
+            state = torch.load(bin_file, map_location="cpu")
+        else:
+            from safetensors.torch import load_file
+            files = [st_file] if os.path.exists(st_file) else glob.glob(os.path.join(pretrained_model_path, "*.safetensors"))
+            for fn in files:
+                state.update(load_file(fn))
+        own = model.state_dict()
+        pw = state.get("patch_embedding.weight")
+        if pw is not None and pw.shape != own["patch_embedding.weight"].shape:  # channel pad/crop (:1294-1300)
+            tgt = torch.zeros_like(own["patch_embedding.weight"])
+            n = min(tgt.shape[1], pw.shape[1])
+            tgt[:, :n] = pw[:, :n]
+            state["patch_embedding.weight"] = tgt
+        state = {k: v for k, v in state.items() if k in own and own[k].shape == v.shape}  # size mismatches skipped
+        missing, unexpected = model.load_state_dict(state, strict=False)
+        print(f"### missing keys: {len(missing)}; \n### unexpected keys: {len(unexpected)};")
+        if geo_changed:  # :240-248
+            nn.init.xavier_uniform_(model.geoada_patch_embedding.weight.data.flatten(1))
+            model.geoada_patch_embedding.bias.data.zero_()
+        return model.to(torch_dtype)
+
+    # -- helpers ------------------------------------------------------------------------------------------------------
+    def _buf(self, name, shape, dtype=torch.bfloat16):
+        t = self._ws.get(name)
+        n = math.prod(shape)
+        if t is None or t.numel() < n or t.dtype != dtype or t.device != self.device:
+            t = torch.empty(n, dtype=dtype, device=self.device)
+            self._ws[name] = t
+        return t[:n].view(shape)
+
+    def release_workspace(self):
+        self._ws.clear()
+
+    def _rope(self, grid):
+        key = (tuple(grid), self.freqs.data_ptr())
+        r = self._rope_cache.get(key)
+        if r is None:
+            c = self.d // 2
+            nh = nw = c // 3
+            nf = c - 2 * (c // 3)
+            cols = torch.split(self.freqs.cpu(), [nf, nh, nw], dim=1)
+            parts = [torch.view_as_real(cols[a][:grid[a]].contiguous()).reshape(-1, 2) for a in range(3)]
+            table = torch.cat(parts).to(torch.float32).to(self.device).contiguous()
+            r = (table, (nf, nh, nw))
+            self._rope_cache = {key: r}
+        return r
+
+    def _time_embed(self, t):
+        """fp32 island (wan_transformer3d_versecrafter.py:347-354).  2 x freq_dim inputs: host-side torch math on a
+        [B, D] problem, not a kernel of the hot path."""
+        half = self.freq_dim // 2
+        pos = t.to(torch.float64)
+        w = torch.pow(torch.tensor(10000.0, dtype=torch.float64, device=t.device),
+                      -torch.arange(half, dtype=torch.float64, device=t.device) / half)
+        ang = pos[:, None] * w[None]
+        s = torch.cat([ang.cos(), ang.sin()], dim=1).float()
+        te0, te2, tp = self.time_embedding[0], self.time_embedding[2], self.time_projection[1]
+        F = torch.nn.functional
+        e = F.linear(F.silu(F.linear(s, te0.weight.float(), te0.bias.float())), te2.weight.float(), te2.bias.float())
+        e0 = F.linear(F.silu(e), tp.weight.float(), tp.bias.float()).unflatten(1, (6, self.dim))
+        return e.to(torch.bfloat16), e0.to(torch.bfloat16)
+
+    def _text_embed(self, context):
+        B = len(context)
+        ctx_in = self._buf("ctx_in", (B * self.text_len, self.text_dim))
+        ctx_in.zero_()
+        v = ctx_in.view(B, self.text_len, self.text_dim)
+        for b, u in enumerate(context):
+            v[b, :u.shape[0]] = u.to(device=self.device, dtype=torch.bfloat16)
+        t0, t2 = self.text_embedding[0], self.text_embedding[2]
+        h = ops.gemm(ctx_in, t0.weight, t0.bias, epilogue=ops.EPI_BIAS | ops.EPI_GELU,
+                     out=self._buf("ctx_h", (B * self.text_len, self.dim)))
+        return ops.gemm(h, t2.weight, t2.bias, out=self._buf("ctx", (B * self.text_len, self.dim)))
+
+    def _patch_embed(self, samples, conv, out, seq_len_p, Lp, name):
+        """Conv3d(kernel=stride=(1,2,2)) as patchify + tcgen05 GEMM; only this rank's token rows are produced; rows
+        past the true length are zero (the reference pads after the conv)."""
+        r0 = self.sp_world_rank * Lp
+        w2d = conv.weight.view(self.dim, -1)
+        for b, u in enumerate(samples):
+            u = u.to(device=self.device, dtype=torch.bfloat16).contiguous()
+            C, Fr, H, W = u.shape
+            L = Fr * (H // 2) * (W // 2)
+            A = ops.patchify(u, out=self._buf(name, (L, 4 * C)))
+            lo, hi = min(r0, L), min(r0 + Lp, L)
+            dst = out[b * Lp:(b + 1) * Lp]
+            if hi > lo:
+                ops.gemm(A[lo:hi], w2d, conv.bias, out=dst[:hi - lo])
+            if hi - lo < Lp:
+                dst[hi - lo:].zero_()
+
+    # -- one DiT block, in place on x2d [B*Lp, D] (wan_transformer3d.py:564-611) ------------------------------------------
+    def _block(self, blk, x2d, m, ctx, st):
+        B, Lp, D, H = st.B, st.Lp, self.dim, self.num_heads
+        rows = B * Lp
+        pk = blk.ensure_packed()
+        sa, ca = blk.self_attn, blk.cross_attn
+        h = self._buf("h", (rows, D))
+        # self-attention half
+        ops.ln_modulate(x2d, m[:, 0], m[:, 1], Lp, eps=self.eps, out=h)
+        qkv = ops.gemm(h, pk["wqkv"], pk["bqkv"], out=self._buf("qkv", (rows, 3 * D)))
+        ops.rmsnorm_rope_(qkv, D, 2, sa.norm_q.weight, sa.norm_k.weight, Lp, eps=self.eps, rope=st.rope, grid=st.grid,
+                          pos_offset=self.sp_world_rank * Lp)
+        attn = self._buf("attn", (rows, D))
+        if self.sp_world_size == 1:
+            q4, k4, v4 = (qkv[:, i * D:(i + 1) * D].view(B, Lp, H, self.d) for i in range(3))
+            if st.k_len < Lp:  # padded tokens are masked as keys (k_lens=seq_lens, :394-399)
+                k4, v4 = k4[:, :st.k_len], v4[:, :st.k_len]
+            ops.flash_attn(q4, k4, v4, out=attn.view(B, Lp, H, self.d), variant=self.attn_variant)
+        else:
+            sp.ulysses_attention(qkv, attn, B, Lp, H, self.d, self.sp_world_size, self.sp_group, self._buf,
+                                 variant=self.attn_variant)
+        ops.gemm(attn, sa.o.weight, sa.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_GATE | ops.EPI_RES, gate=m[:, 2],
+                 rows_per_batch=Lp, residual=x2d, out=x2d)
+        # cross-attention
+        ops.ln_affine(x2d, blk.norm3.weight, blk.norm3.bias, eps=self.eps, out=h)
+        qc = ops.gemm(h, ca.q.weight, ca.q.bias, out=self._buf("qc", (rows, D)))
+        ops.rmsnorm_rope_(qc, D, 1, ca.norm_q.weight, None, Lp, eps=self.eps)
+        T = ctx.shape[0] // B
+        kv = ops.gemm(ctx, pk["wkv"], pk["bkv"], out=self._buf("kv", (B * T, 2 * D)))
+        ops.rmsnorm_rope_(kv, D, 1, ca.norm_k.weight, None, T, eps=self.eps)
+        ops.flash_attn(qc.view(B, Lp, H, self.d), kv[:, :D].view(B, T, H, self.d), kv[:, D:].view(B, T, H, self.d),
+                       out=attn.view(B, Lp, H, self.d), variant=self.attn_variant)
+        ops.gemm(attn, ca.o.weight, ca.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_RES, residual=x2d, out=x2d)
+        # FFN half
+        ops.ln_modulate(x2d, m[:, 3], m[:, 4], Lp, eps=self.eps, out=h)
+        f1, f2 = blk.ffn[0], blk.ffn[2]
+        hid = ops.gemm(h, f1.weight, f1.bias, epilogue=ops.EPI_BIAS | ops.EPI_GELU,
+                       out=self._buf("ffn", (rows, self.ffn_dim)))
+        ops.gemm(hid, f2.weight, f2.bias, epilogue=ops.EPI_BIAS | ops.EPI_GATE | ops.EPI_RES, gate=m[:, 5],
+                 rows_per_batch=Lp, residual=x2d, out=x2d)
+        return x2d
+
+    def _geo_block(self, j, c2d, x2d, e0, ctx, st):
+        """GeoAdapter block j on the control stream c (VerseCrafterWanAttentionBlock.forward :112-125)."""
+        blk = self.geoada_blocks[j]
+        if j == 0:  # c = before_proj(c) + x   (x is still the embedded tokens x0 here)
+            bp = blk.before_proj
+            ops.gemm(c2d, bp.weight, bp.bias, epilogue=ops.EPI_BIAS | ops.EPI_RES, residual=x2d, out=c2d)
+        if self.record is not None:
+            self.record[f"geo_in.{j}"] = c2d.view(st.B, st.Lp, -1).clone()
+        m = (blk.modulation + e0).to(torch.bfloat16)
+        self._block(blk, c2d, m, ctx, st)
+        if self.record is not None:
+            self.record[f"geo_out.{j}"] = c2d.view(st.B, st.Lp, -1).clone()
+
+    def _run_blocks(self, x2d, c2d, e0, ctx, st, scale):
+        """Backbone with the GeoAdapter interleaved: geo block j executes right before the layer that consumes its
+        hint; `x += scale * after_proj(c)` is the after_proj GEMM's epilogue (wan_transformer3d_versecrafter.py:121,
+        :144-148).  Arbitrary (also unsorted) geoada_layers are handled by materialising run-ahead hints."""
+        next_geo, stored = 0, {}
+        for i, blk in enumerate(self.blocks):
+            j = self.geoada_layers_mapping.get(i)
+            if j is not None:
+                while next_geo <= j:
+                    self._geo_block(next_geo, c2d, x2d, e0, ctx, st)
+                    if next_geo < j:  # consumed later: keep the hint (only for non-monotone layer lists)
+                        ap = self.geoada_blocks[next_geo].after_proj
+                        stored[next_geo] = ops.gemm(c2d, ap.weight, ap.bias)
+                    next_geo += 1
+            if self.record is not None:
+                self.record[f"blk_in.{i}"] = x2d.view(st.B, st.Lp, -1).clone()
+            m = (blk.modulation + e0).to(torch.bfloat16)
+            self._block(blk, x2d, m, ctx, st)
+            if j is not None:
+                if j in stored:
+                    hint = stored.pop(j)
+                    x2d.add_((hint * scale).to(torch.bfloat16))
+                elif j == next_geo - 1:
+                    ap = self.geoada_blocks[j].after_proj
+                    if self.record is not None:
+                        self.record[f"hint.{j}"] = ops.gemm(c2d, ap.weight, ap.bias).view(st.B, st.Lp, -1)
+                    ops.gemm(c2d, ap.weight, ap.bias, epilogue=ops.EPI_BIAS | ops.EPI_SCALE | ops.EPI_RES,
+                             residual=x2d, scale=float(scale), out=x2d)
+                else:  # geo block j ran earlier for a smaller layer index and c has moved on
+                    raise VCError("internal: hint ordering")
+            if self.record is not None:
+                self.record[f"blk_out.{i}"] = x2d.view(st.B, st.Lp, -1).clone()
+        return x2d
+
+    @torch.no_grad()
+    def block_forward(self, kind, idx, x, e0, ctx, grid):
+        """Teacher-forced single block for the parity tests: kind 'blocks' | 'geoada_blocks', x [B, L, D] (copied),
+        e0 [B, 6, D], ctx [B, T, D] (embedded text).  Returns the block output WITHOUT hint/after_proj."""
+        B, L, D = x.shape
+        blk = getattr(self, kind)[idx]
+        st = SimpleNamespace(B=B, Lp=L, grid=tuple(grid), rope=self._rope(tuple(grid)), k_len=L)
+        x2d = x.to(torch.bfloat16).reshape(B * L, D).clone()
+        m = (blk.modulation + e0.to(torch.bfloat16)).to(torch.bfloat16)
+        self._block(blk, x2d, m, ctx.to(torch.bfloat16).reshape(-1, D).contiguous(), st)
+        return x2d.view(B, L, D)
+
+    # -- forward (wan_transformer3d_versecrafter.py:294-442) -----------------------------------------------------------------
+    @torch.no_grad()
+    def forward(self, x, t, geoada_context, context, seq_len, geoada_context_scale=1.0, clip_fea=None, y=None,
+                cond_flag=True):
+        # cfg-skip (videox_fun.utils.cfg_skip, recalled contract SURVEY App. A.11): late steps run the second half only
+        if self.cfg_skip_ratio is not None and self.num_inference_steps is not None and len(x) > 1 and \
+                self.current_steps >= self.num_inference_steps * (1 - self.cfg_skip_ratio):
+            half = len(x) // 2
+            out = self._forward([u for u in x][half:], t[half:], [u for u in geoada_context][half:],
+                                list(context)[half:], seq_len, geoada_context_scale, cond_flag)
+            return torch.cat([out, out], dim=0)
+        return self._forward(x, t, geoada_context, context, seq_len, geoada_context_scale, cond_flag)
+
+    def _forward(self, x, t, geoada_context, context, seq_len, scale, cond_flag):
+        if self.device.type != "cuda":
+            raise VCError("VerseCrafterWanTransformer3DModel (B200) runs on CUDA only; there is no CPU fallback")
+        if self.dtype != torch.bfloat16:
+            raise VCError(f"parameters must be bf16 (got {self.dtype}); use .to(torch.bfloat16)")
+        samples = [u for u in x]
+        B = len(samples)
+        P = self.sp_world_size
+        Fr, Hh, Ww = samples[0].shape[1:]
+        grid = (Fr, Hh // 2, Ww // 2)
+        L = grid[0] * grid[1] * grid[2]
+        for u in samples:
+            assert tuple(u.shape[1:]) == (Fr, Hh, Ww), "all samples of a batch share one latent shape"
+        seq_len_p = int(math.ceil(seq_len / P)) * P
+        assert L <= seq_len_p, "sequence longer than seq_len"  # wan_transformer3d.py:197
+        Lp = seq_len_p // P
+        st = SimpleNamespace(B=B, Lp=Lp, grid=grid, rope=self._rope(grid), k_len=L if P == 1 else Lp)
+        D = self.dim
+
+        x2d = self._buf("x", (B * Lp, D))
+        self._patch_embed(samples, self.patch_embedding, x2d, seq_len_p, Lp, "pe_a")
+        t = t.to(self.device)
+        e, e0 = self._time_embed(t)
+        ctx = self._text_embed(context)
+        if self.record is not None:
+            self.record.update(x0=x2d.view(B, Lp, D).clone(), e=e, e0=e0, ctx=ctx.view(B, -1, D).clone())
+
+        should_calc = True
+        if self.teacache is not None:
+            should_calc = self._teacache_decide(e0, t, cond_flag)
+        if should_calc:
+            c2d = self._buf("c", (B * Lp, D))
+            self._patch_embed([u for u in geoada_context], self.geoada_patch_embedding, c2d, seq_len_p, Lp, "ge_a")
+            ori = x2d.clone() if self.teacache is not None else None
+            self._run_blocks(x2d, c2d, e0, ctx, st, scale)
+            if self.teacache is not None:
+                res = x2d - ori
+                res = res.cpu() if self.teacache.offload else res
+                if cond_flag:
+                    self.teacache.previous_residual_cond = res
+                else:
+                    self.teacache.previous_residual_uncond = res
+        else:
+            prev = self.teacache.previous_residual_cond if cond_flag else self.teacache.previous_residual_uncond
+            x2d.add_(prev.to(x2d.device)[-x2d.shape[0]:])
+
+        # head (wan_transformer3d.py:631-644)
+        mh = (self.head.modulation + e[:, None, :]).to(torch.bfloat16)
+        hh = ops.ln_modulate(x2d, mh[:, 0], mh[:, 1], Lp, eps=self.eps, out=self._buf("h", (B * Lp, D)))
+        yv = ops.gemm(hh, self.head.head.weight, self.head.head.bias).view(B, Lp, -1)
+        if self.record is not None:
+            self.record["head"] = yv
+        if P > 1:
+            yv = self.all_gather(yv, dim=1)
+        out = torch.stack([ops.unpatchify(yv[b], grid, self.out_dim) for b in range(B)])
+        if self.teacache is not None and cond_flag:
+            self.teacache.cnt += 1
+            if self.teacache.cnt == self.teacache.num_steps:
+                self.teacache.reset()
+        return out
+
+    def _teacache_decide(self, e0, t, cond_flag):
+        tc = self.teacache
+        if not cond_flag:
+            return tc.should_calc
+        inp = e0[:, -1, :] if t.dim() != 1 else e0
+        if tc.cnt < tc.num_skip_start_steps or tc.previous_modulated_input is None:
+            calc = True
+            tc.accumulated_rel_l1_distance = 0
+        else:
+            tc.accumulated_rel_l1_distance += tc.rescale_func(tc.compute_rel_l1_distance(tc.previous_modulated_input, inp))
+            calc = not (tc.accumulated_rel_l1_distance < tc.rel_l1_thresh)
+            if calc:
+                tc.accumulated_rel_l1_distance = 0
+        tc.previous_modulated_input = inp
+        tc.should_calc = calc
+        return calc
