@@ -1,0 +1,54 @@
+"""Host-side logic of the Ulysses path on CPU: 2 processes over gloo.  Checks that scatter_heads / gather_heads are
+the all-to-all permutations the sequence-parallel attention needs (equal to slicing the un-sharded tensor) and that
+an attention computed on [all tokens, my heads] and gathered back equals the single-process result."""
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import restate
+        from versecrafter_b200 import sp
+        B, L, H, d = 2, 12, 4, 8
+        g = torch.Generator().manual_seed(0)
+        q, k, v = (torch.randn(B, L, H, d, generator=g) for _ in range(3))
+        Lp, Hp = L // world, H // world
+        mine = slice(rank * Lp, (rank + 1) * Lp)
+        heads = slice(rank * Hp, (rank + 1) * Hp)
+        qs = sp.scatter_heads(q[:, mine].contiguous(), world)
+        assert torch.equal(qs, q[:, :, heads]), "scatter_heads != slicing"
+        ks, vs = sp.scatter_heads(k[:, mine].contiguous(), world), sp.scatter_heads(v[:, mine].contiguous(), world)
+        o_local = restate.sdpa(qs, ks, vs)                      # my heads, all tokens
+        o = sp.gather_heads(o_local, world)                     # all heads, my tokens
+        want = restate.sdpa(q, k, v)[:, mine]
+        assert torch.allclose(o, want, atol=1e-5), "ulysses attention != single-process attention"
+        full = sp.all_gather_tokens(want.contiguous(), 1)
+        assert torch.allclose(full, restate.sdpa(q, k, v), atol=1e-5)
+        ret[rank] = "ok"
+    except Exception as e:  # noqa: BLE001
+        ret[rank] = repr(e)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_ulysses_layouts_world2():
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(2, port, ret), nprocs=2, join=True)
+    assert dict(ret) == {0: "ok", 1: "ok"}, dict(ret)
+
+
+def test_bench_work_formula_matches_survey():
+    import bench
+    cfg, grid, _ = bench.CONFIGS["c3"]
+    gemm, attn = bench.work_per_step(cfg, 32760, 2)
+    assert abs(gemm / 1e15 - 2.429) < 0.01 and abs(attn / 1e15 - 2.679) < 0.01
