@@ -1,0 +1,43 @@
+"""Run under torchrun on N GPUs: the Ulysses sequence-parallel forward must equal the single-GPU forward of the same
+model and inputs (P-invariance).  Every rank holds the full weights, so each rank computes the
+P=1 result locally and compares it with the gathered SP result."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from versecrafter_b200.transformer import VerseCrafterWanTransformer3DModel  # noqa: E402
+
+
+def main():
+    rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    cfg = dict(dim=1024, ffn_dim=2048, num_heads=8, num_layers=2, text_dim=256, geoada_in_dim=128)
+    grid = (4, 32, 48)  # L = 1536, divisible by 8
+    model = VerseCrafterWanTransformer3DModel(**cfg, device="cuda", dtype=torch.bfloat16, init=False).synthetic_init_(0)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(2, 16, *grid, generator=g, device="cuda").bfloat16()
+    geo = torch.randn(2, 128, *grid, generator=g, device="cuda").bfloat16()
+    ctx = [torch.randn(n, 256, generator=g, device="cuda").bfloat16() * 0.1 for n in (37, 512)]
+    t = torch.full((2,), 500.0, device="cuda")
+    L = grid[0] * grid[1] * grid[2] // 4
+    y1 = model(x, t, geo, ctx, L).float()
+    model.enable_multi_gpus_inference()
+    yp = model(x, t, geo, ctx, L).float()
+    torch.cuda.synchronize()
+    cos = float(torch.nn.functional.cosine_similarity(y1.flatten().double(), yp.flatten().double(), dim=0))
+    rel = float((y1 - yp).norm() / y1.norm())
+    ok = cos > 0.9999 and rel < 1e-2
+    flags = torch.tensor([1.0 if ok else 0.0], device="cuda")
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print(f"sp_check world={world}: cosine {cos:.7f} rel-L2 {rel:.5f} -> {'OK' if flags.item() == 1 else 'FAIL'}", flush=True)
+    dist.destroy_process_group()
+    sys.exit(0 if flags.item() == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -208,9 +208,13 @@ flash_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             if (i >= valid) s[i] = __float_as_uint(-INFINITY);
         }
       }
-      float mt = __uint_as_float(s[0]);
+      // 8 independent max chains (a single 127-deep dependent FMNMX chain costs ~500 cycles of pure latency)
+      float mx[8];
 #pragma unroll
-      for (int i = 1; i < 128; ++i) mt = fmaxf(mt, __uint_as_float(s[i]));
+      for (int i = 0; i < 8; ++i) mx[i] = __uint_as_float(s[i]);
+#pragma unroll
+      for (int i = 8; i < 128; ++i) mx[i & 7] = fmaxf(mx[i & 7], __uint_as_float(s[i]));
+      const float mt = fmaxf(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])), fmaxf(fmaxf(mx[4], mx[5]), fmaxf(mx[6], mx[7])));
       const float m_new = fmaxf(m_run, mt);
       const bool need = (m_new - m_run) * sl2 > RESCALE_THRESHOLD;  // true on the first tile (m_run = -inf)
       if (__any_sync(0xffffffffu, need)) {
@@ -234,13 +238,16 @@ flash_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
       const float mb = m_run * sl2;
       float sum = 0.f;
       if (kPInTmem) {
+        float sum1 = 0.f;
 #pragma unroll
         for (int i = 0; i < 64; ++i) {
           const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -mb));
           const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -mb));
-          sum += p0 + p1;
+          sum += p0;
+          sum1 += p1;
           s[i] = vc::pack_bf16x2(p0, p1);
         }
+        sum += sum1;
         vc::tmem_st32(s_addr, s);
         vc::tmem_st32(s_addr + 32, s + 32);
         vc::tmem_st_wait();
