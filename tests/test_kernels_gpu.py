@@ -43,6 +43,21 @@ def test_ln_modulate(ops, D, rows_per_batch):
     assert (out.float() - ref.float()).abs().max() <= 0.07 * ref.float().abs().max()
 
 
+@pytest.mark.parametrize("D", [1032, 3072, 4096, 6144, 8192])
+def test_ln_modulate_wide_rows(ops, D):
+    """Block-per-row kernel (D > 1024) at every vectors-per-thread instantiation, incl. a ragged last vector group,
+    and more rows than resident CTAs so the grid-stride loop (and its shared-memory reuse) is exercised."""
+    B, rpb = 2, 2500
+    x = _rand((B, rpb, D), 21, 2.0) + 0.5
+    m = _rand((B, 6, D), 22, 0.3)
+    out = ops.ln_modulate(x, m[:, 3], m[:, 4], rpb)
+    ref = restate.layer_norm(x) * (1 + m[:, 4:5]) + m[:, 3:4]
+    assert relerr(out, ref) < 4e-3
+    gamma = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    beta = (0.02 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    assert relerr(ops.ln_affine(x, gamma, beta), restate.layer_norm(x, gamma, beta)) < 4e-3
+
+
 @pytest.mark.parametrize("D", [128, 1536, 5120])
 def test_ln_affine(ops, D):
     x = _rand((3, 50, D), 3, 1.5)
@@ -76,6 +91,27 @@ def test_rmsnorm_rope(ops, D, H, grid, pos_offset, rows_per_batch):
         want = restate.rope_rotate(full, ang)[:, pos_offset:pos_offset + rows_per_batch]
         got = qkv[:, i * D:(i + 1) * D].view(B, rows_per_batch, H, d)
         assert relerr(got, want) < 4e-3, i
+    assert torch.equal(qkv[:, 2 * D:], ref_in[:, 2 * D:])
+
+
+@pytest.mark.parametrize("D,H", [(3072, 24), (4096, 32), (8192, 64)])
+def test_rmsnorm_rope_wide_rows(ops, D, H):
+    """Block-per-row kernel with the grid-stride loop active (rows > resident CTAs), q and k, SP position offset."""
+    B, grid, pos_offset = 2, (5, 20, 30), 1500
+    rpb, d = 1500, D // H
+    qkv = _rand((B * rpb, 3 * D), 23)
+    gq = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    gk = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    ref_in = qkv.clone()
+    rope = ops.rope_table(d, grid, "cuda")
+    ops.rmsnorm_rope_(qkv, D, 2, gq, gk, rpb, rope=rope, grid=grid, pos_offset=pos_offset)
+    ang = restate.rope_angles(d, grid, device="cuda")
+    for i, g in enumerate((gq, gk)):
+        u = restate.rms_norm(ref_in[:, i * D:(i + 1) * D], g).view(B, rpb, H, d)
+        full = torch.zeros(B, pos_offset + rpb, H, d, dtype=u.dtype, device="cuda")
+        full[:, pos_offset:] = u
+        want = restate.rope_rotate(full, ang)[:, pos_offset:]
+        assert relerr(qkv[:, i * D:(i + 1) * D].view(B, rpb, H, d), want) < 4e-3, i
     assert torch.equal(qkv[:, 2 * D:], ref_in[:, 2 * D:])
 
 

@@ -25,6 +25,15 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {
                : "l"(p));
   return r;
 }
+// same, for buffers this kernel also writes (in-place RMSNorm/RoPE): no .nc
+__device__ __forceinline__ uint4 ld_stream_rw(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];\n"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
 __device__ __forceinline__ void st_stream(uint4* p, const uint4& v) {
   asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};\n" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
                "r"(v.w)
@@ -196,6 +205,165 @@ __global__ void __launch_bounds__(256) rmsnorm_rope_kernel(__nv_bfloat16* __rest
 }
 
 // ----------------------------------------------------------------------------------------------------
+// Wide rows (D > 1024): one 128-thread CTA per row, VPT 16-byte vectors per thread (5 at D = 5120), so a thread holds
+// 20 data registers instead of 80 and 8+ CTAs stay resident per SM — enough loads in flight to cover HBM latency.
+// Cross-warp sums go through two tiny shared arrays (one __syncthreads each).
+// ----------------------------------------------------------------------------------------------------
+constexpr int ROW_NT = 128;
+
+__device__ __forceinline__ float block_sum(float v, float* red) {  // red: ROW_NT/32 floats, reused only after a sync
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+#pragma unroll
+  for (int i = 0; i < ROW_NT / 32; ++i) t += red[i];
+  return t;
+}
+
+template <int VPT>
+__global__ void __launch_bounds__(ROW_NT, VPT <= 4 ? 8 : 7) ln_modulate_block_kernel(
+    const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ p0,
+    const __nv_bfloat16* __restrict__ p1, long long mod_stride, long long rows, long long rows_per_batch, int D,
+    long long ldx, long long ldo, float eps, int mode) {
+  __shared__ float red_a[ROW_NT / 32], red_b[ROW_NT / 32];
+  const int nvec = D >> 3;
+  const float inv_d = 1.0f / (float)D;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const uint4* xr = reinterpret_cast<const uint4*>(x + row * ldx);
+    uint4 raw[VPT];
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + ROW_NT * i;
+      raw[i] = (v < nvec) ? ld_stream(xr + v) : make_uint4(0, 0, 0, 0);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      float f[8];
+      unpack8(raw[i], f);
+      s += ((f[0] + f[1]) + (f[2] + f[3])) + ((f[4] + f[5]) + (f[6] + f[7]));
+    }
+    const float mean = block_sum(s, red_a) * inv_d;
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      if (threadIdx.x + ROW_NT * i < nvec) {
+        float f[8];
+        unpack8(raw[i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = f[j] - mean;
+          ss = fmaf(d, d, ss);
+        }
+      }
+    }
+    const float rstd = rsqrtf(block_sum(ss, red_b) * inv_d + eps);
+    const long long moff = (mode == 0) ? (row / rows_per_batch) * mod_stride : 0;
+    const uint4* q0 = reinterpret_cast<const uint4*>(p0 + moff);
+    const uint4* q1 = reinterpret_cast<const uint4*>(p1 + moff);
+    uint4* orow = reinterpret_cast<uint4*>(out + row * ldo);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + ROW_NT * i;
+      if (v < nvec) {
+        float f[8], a[8], c[8];
+        unpack8(raw[i], f);
+        unpack8(__ldg(q0 + v), a);
+        unpack8(__ldg(q1 + v), c);
+        if (mode == 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float ln = bf16_round((f[j] - mean) * rstd);
+            const float sc = bf16_round(1.0f + c[j]);
+            f[j] = bf16_round(ln * sc) + a[j];
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = (f[j] - mean) * rstd * c[j] + a[j];
+        }
+        st_stream(orow + v, pack8(f));
+      }
+    }
+  }
+}
+
+// Requires (ROW_NT * 8) % head_dim == 0 when rotating: every vector of a thread then sits at the same offset inside
+// its head, so the 4 (cos, sin) pairs are fetched once per row and reused for all VPT vectors and for q and k.
+template <int VPT>
+__global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_block_kernel(
+    __nv_bfloat16* __restrict__ qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset, int D,
+    const __nv_bfloat16* __restrict__ gq, const __nv_bfloat16* __restrict__ gk, const float2* __restrict__ tab, int Fg,
+    int Hg, int Wg, int nf, int nh, int nw, float eps, int do_rope, int n_mats) {
+  __shared__ float red_a[ROW_NT / 32], red_b[ROW_NT / 32];
+  const int nvec = D >> 3;
+  const float inv_d = 1.0f / (float)D;
+  const int half_d = nf + nh + nw;
+  const float2* tab_f = tab;
+  const float2* tab_h = tab + (long long)Fg * nf;
+  const float2* tab_w = tab_h + (long long)Hg * nh;
+  const int j0 = do_rope ? (((threadIdx.x * 8) % (2 * half_d)) >> 1) : 0;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const long long pos = pos_offset + (row % rows_per_batch);
+    const bool rot = do_rope && pos < (long long)Fg * Hg * Wg;
+    float2 cs[4];
+    if (rot) {
+      const int pw = (int)(pos % Wg);
+      const int ph = (int)((pos / Wg) % Hg);
+      const int pf = (int)(pos / ((long long)Wg * Hg));
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const int j = j0 + p;
+        if (j < nf) cs[p] = __ldg(tab_f + pf * nf + j);
+        else if (j < nf + nh) cs[p] = __ldg(tab_h + ph * nh + (j - nf));
+        else cs[p] = __ldg(tab_w + pw * nw + (j - nf - nh));
+      }
+    }
+#pragma unroll 1
+    for (int which = 0; which < n_mats; ++which) {
+      uint4* xr = reinterpret_cast<uint4*>(qkv + row * ld + (long long)which * D);
+      const uint4* gr = reinterpret_cast<const uint4*>(which == 0 ? gq : gk);
+      uint4 raw[VPT];
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + ROW_NT * i;
+        raw[i] = (v < nvec) ? ld_stream_rw(xr + v) : make_uint4(0, 0, 0, 0);
+      }
+      float ss = 0.f;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        float f[8];
+        unpack8(raw[i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss = fmaf(f[j], f[j], ss);
+      }
+      const float r = bf16_round(rsqrtf(block_sum(ss, which ? red_b : red_a) * inv_d + eps));
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + ROW_NT * i;
+        if (v < nvec) {
+          float f[8], g[8];
+          unpack8(raw[i], f);
+          unpack8(__ldg(gr + v), g);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = bf16_round(bf16_round(f[j] * r) * g[j]);
+          if (rot) {
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+              const float a = f[2 * p], b = f[2 * p + 1];
+              f[2 * p] = a * cs[p].x - b * cs[p].y;
+              f[2 * p + 1] = a * cs[p].y + b * cs[p].x;
+            }
+          }
+          st_stream(xr + v, pack8(f));
+        }
+      }
+      if (n_mats == 1) __syncthreads();  // red_a is reused by the next row
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------
 // patchify: [C, F, H, W] bf16 (one sample) -> A[L, C*4] bf16, K ordered (c, ph, pw)  (SURVEY App. A.1).
 // Feeds the tcgen05 GEMM that implements the Conv3d patch embedding (stride == kernel, so it is a pure GEMM).
 // thread -> (token, c): reads two 4-byte pairs (rows 2h, 2h+1), writes 8 contiguous bytes.
@@ -253,6 +421,23 @@ int dispatch_vpl(int D, F&& f) {
   return -1;
 }
 
+template <typename F>
+int dispatch_vpt(int D, F&& f) {  // block-per-row kernels: vectors per thread at ROW_NT threads
+  const int need = (D / 8 + ROW_NT - 1) / ROW_NT;
+  if (need <= 2) return f(std::integral_constant<int, 2>{});
+  if (need <= 3) return f(std::integral_constant<int, 3>{});
+  if (need <= 4) return f(std::integral_constant<int, 4>{});
+  if (need <= 5) return f(std::integral_constant<int, 5>{});
+  if (need <= 6) return f(std::integral_constant<int, 6>{});
+  if (need <= 8) return f(std::integral_constant<int, 8>{});
+  return -1;
+}
+
+int grid_for_block_rows(long long rows) {
+  const long long cap = 148LL * 16;  // up to 16 resident 128-thread CTAs per SM
+  return (int)(rows < cap ? (rows < 1 ? 1 : rows) : cap);
+}
+
 int grid_for_rows(long long rows, int warps_per_cta) {
   long long ctas = (rows + warps_per_cta - 1) / warps_per_cta;
   const long long cap = 148LL * 8;  // 8 resident 256-thread CTAs per SM
@@ -271,6 +456,17 @@ int vc_ln_modulate(const void* x, long long ldx, void* out, long long ldo, const
   VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && ldx % 8 == 0 && ldo % 8 == 0, "vc_ln_modulate: bad rows/strides");
   VC_CHECK_ARG(mode == 0 || mode == 1, "vc_ln_modulate: mode must be 0 (modulate) or 1 (affine)");
   if (rows == 0) return 0;
+  if (D > 1024) {
+    int rcb = dispatch_vpt(D, [&](auto vpt) {
+      constexpr int V = decltype(vpt)::value;
+      ln_modulate_block_kernel<V><<<grid_for_block_rows(rows), ROW_NT, 0, (cudaStream_t)stream>>>(
+          (const __nv_bfloat16*)x, (__nv_bfloat16*)out, (const __nv_bfloat16*)shift_or_beta,
+          (const __nv_bfloat16*)scale_or_gamma, mod_batch_stride, rows, rows_per_batch, D, ldx, ldo, eps, mode);
+      return 0;
+    });
+    VC_CHECK_ARG(rcb == 0, "vc_ln_modulate: unsupported D=%d", D);
+    VC_RETURN_LAUNCH_STATUS("vc_ln_modulate");
+  }
   int rc = dispatch_vpl(D, [&](auto vpl) {
     constexpr int V = decltype(vpl)::value;
     ln_modulate_kernel<V><<<grid_for_rows(rows, 8), 256, 0, (cudaStream_t)stream>>>(
@@ -293,6 +489,18 @@ int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_p
                "vc_rmsnorm_rope_qk: bad rope table split");
   VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && pos_offset >= 0, "vc_rmsnorm_rope_qk: bad rows");
   if (rows == 0) return 0;
+  if (D > 1024 && (!apply_rope || (ROW_NT * 8) % (2 * (nf + nh + nw)) == 0)) {
+    int rcb = dispatch_vpt(D, [&](auto vpt) {
+      constexpr int V = decltype(vpt)::value;
+      rmsnorm_rope_block_kernel<V><<<grid_for_block_rows(rows), ROW_NT, 0, (cudaStream_t)stream>>>(
+          (__nv_bfloat16*)qkv, ld, rows, rows_per_batch, pos_offset, D, (const __nv_bfloat16*)gain_q,
+          (const __nv_bfloat16*)gain_k, (const float2*)rope_table, grid_f, grid_h, grid_w, nf, nh, nw, eps, apply_rope,
+          n_mats);
+      return 0;
+    });
+    VC_CHECK_ARG(rcb == 0, "vc_rmsnorm_rope_qk: unsupported D=%d", D);
+    VC_RETURN_LAUNCH_STATUS("vc_rmsnorm_rope_qk");
+  }
   int rc = dispatch_vpl(D, [&](auto vpl) {
     constexpr int V = decltype(vpl)::value;
     rmsnorm_rope_kernel<V><<<grid_for_rows(rows, 8), 256, 0, (cudaStream_t)stream>>>(
