@@ -64,8 +64,12 @@ int vc_gemm_bf16(const void* A, long long lda, const void* W, long long ldw, voi
 /* K6/K7 — o = softmax(q k^T * softmax_scale) v, non-causal, all Lk keys attended (no mask other than the tail of
  * the last 128-key tile).  Replaces videox_fun attention() at wan_transformer3d.py:394-399 (self) and :425-430
  * (cross).  head_dim must be 128 and contiguous; *_strides = {batch, token, head} strides in elements (so q/k/v
- * may be column slices of one fused QKV buffer).  variant 0: P staged through shared memory (SS MMA);
- * variant 1: P kept in tensor memory (TS MMA). */
+ * may be column slices of one fused QKV buffer).  variant selects the kernel schedule (same arithmetic):
+ *   0: P staged through shared memory (SS MMA);  1: P written over S in tensor memory (TS MMA);
+ *   2: one S buffer shared by both Q tiles, P in its own TMEM columns (S_j+1 overlaps softmax_j);
+ *   3: 2 + split PV issue + packed fp32x2 softmax;  4 / 5: 3 + 16 / 32 of every 128 exp2 evaluated by a
+ *   degree-3 polynomial on the FMA pipe instead of the MUFU (rel. error < 1e-4, below P's bf16 rounding).
+ *   4 is the fastest on B200 under the power cap and is what the drop-in module uses. */
 int vc_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, int B, int H, int Lq, int Lk,
                       int head_dim, const long long* q_strides, const long long* k_strides,
                       const long long* v_strides, const long long* o_strides, float softmax_scale, int variant,

@@ -213,6 +213,15 @@ def test_flash_attn_tmem_p(ops, B, H, Lq, Lk):
     assert _attn_case(ops, B, H, Lq, Lk, 1, True) < 1e-2
 
 
+@pytest.mark.parametrize("B,H,Lq,Lk", ATTN_SHAPES + [(1, 2, 1000, 2600), (2, 1, 640, 128)])
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("variant", [2, 3, 4, 5])
+def test_flash_attn_shared_s(ops, B, H, Lq, Lk, fused, variant):
+    """variants 2-5: one S buffer shared by both Q tiles, P in its own TMEM columns (odd/even tile counts, tails);
+    3 = split PV issue + packed fp32x2 softmax, 4 / 5 = 16 / 32 of every 128 exp2 on the FMA pipe (polynomial)."""
+    assert _attn_case(ops, B, H, Lq, Lk, variant, fused) < 1e-2
+
+
 def test_flash_attn_large_scores_rescale(ops):
     """Rows whose running max keeps growing across key tiles exercise the O rescale path."""
     B, H, L, d = 1, 1, 1024, 128
@@ -220,8 +229,8 @@ def test_flash_attn_large_scores_rescale(ops):
     k = _rand((B, L, H, d), 26, 1.0)
     k = (k.float() * torch.linspace(0.2, 3.0, L, device="cuda")[None, :, None, None]).to(torch.bfloat16)
     v = _rand((B, L, H, d), 27)
-    for variant in (0,):
-        assert relerr(ops.flash_attn(q, k, v, variant=variant), restate.sdpa(q, k, v)) < 1e-2
+    for variant in (0, 1, 2, 3, 4, 5):
+        assert relerr(ops.flash_attn(q, k, v, variant=variant), restate.sdpa(q, k, v)) < 1e-2, variant
 
 
 def test_patchify_unpatchify(ops):

@@ -106,6 +106,36 @@ def bench_attn(B, H, Lq, Lk, variant):
     emit(rec)
 
 
+def bench_attn_sustained(variant, seconds=4.0, B=2, H=40, L=32760):
+    """c3 self-attention launched back to back for a few seconds: throughput under the 1 kW power cap (what the
+    kernel delivers inside a long denoise step), not the burst figure."""
+    q = torch.randn(B, L, H, 128, device="cuda", dtype=torch.bfloat16)
+    k = torch.randn(B, L, H, 128, device="cuda", dtype=torch.bfloat16)
+    v = torch.randn(B, L, H, 128, device="cuda", dtype=torch.bfloat16)
+    out = torch.empty_like(q)
+    ops.flash_attn(q, k, v, out=out, variant=variant)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    ops.flash_attn(q, k, v, out=out, variant=variant)
+    e1.record()
+    torch.cuda.synchronize()
+    n = max(4, int(seconds * 1e3 / e0.elapsed_time(e1)))
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(n + 1)]
+    ev[0].record()
+    for i in range(n):
+        ops.flash_attn(q, k, v, out=out, variant=variant)
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ts = [ev[i].elapsed_time(ev[i + 1]) for i in range(n)]
+    flops = 4.0 * B * H * L * L * 128
+    last = ts[len(ts) // 2:]
+    emit(dict(kernel=f"flash_attn_v{variant}_sustained", shape=[B, H, L, L], launches=n, ms_first=ts[0],
+              ms_last_half=sum(last) / len(last), tflops_first=flops / ts[0] / 1e9,
+              tflops_last_half=flops / (sum(last) / len(last)) / 1e9,
+              frac_bf16_sustained=flops / (sum(last) / len(last)) / 1e9 / PEAKS["bf16_tflops_sustained"]))
+
+
 if __name__ == "__main__":
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
     which = sys.argv[1:] or ["rows", "gemm", "attn"]
@@ -117,6 +147,9 @@ if __name__ == "__main__":
         for (N, K, epi) in [(15360, 5120, "bias"), (5120, 5120, "gate_res"), (13824, 5120, "gelu"), (5120, 13824, "gate_res"),
                             (5120, 512, "bias"), (4608, 1536, "bias")]:
             bench_gemm(M, N, K, epi)
+    if "attn_sustained" in which:
+        for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "1,2").split(",")]:
+            bench_attn_sustained(variant)
     if "attn" in which:
         for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "0,1").split(",")]:
             bench_attn(1, 8, 32760, 32760, variant)

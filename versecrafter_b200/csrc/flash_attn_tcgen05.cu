@@ -46,6 +46,43 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// packed fp32x2 arithmetic (sm_100 FFMA2 / FADD2): one issue slot for two lanes of the softmax row
+__device__ __forceinline__ void ffma2(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0, float c1) {
+  asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rc, {%6, %7};\n\t"
+      "fma.rn.ftz.f32x2 rd, ra, rb, rc;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}\n"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
+__device__ __forceinline__ void fadd2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+      "add.rn.ftz.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}\n"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+// 2^x for two values on the FMA/ALU pipes instead of the MUFU (Cody-Waite split + degree-3 minimax polynomial for
+// 2^f on [0,1), rel. error < 1e-4: below the bf16 rounding of P).  x <= ~8 here; clamped at -126.
+__device__ __forceinline__ void exp2_poly2(float& r0, float& r1, float x0, float x1) {
+  constexpr float MAGIC = 12582912.0f;  // 1.5 * 2^23: x + MAGIC (round toward -inf) holds floor(x) in the low mantissa
+  x0 = fmaxf(x0, -126.0f);
+  x1 = fmaxf(x1, -126.0f);
+  float t0, t1;
+  asm("add.rm.ftz.f32 %0, %1, %2;" : "=f"(t0) : "f"(x0), "f"(MAGIC));
+  asm("add.rm.ftz.f32 %0, %1, %2;" : "=f"(t1) : "f"(x1), "f"(MAGIC));
+  float fl0, fl1, f0, f1;
+  fadd2(fl0, fl1, t0, t1, -MAGIC, -MAGIC);   // floor(x)
+  fadd2(f0, f1, x0, x1, -fl0, -fl1);         // fractional part in [0, 1)
+  float p0, p1;
+  ffma2(p0, p1, f0, f1, 0.07802334f, 0.07802334f, 0.22606642f, 0.22606642f);
+  ffma2(p0, p1, p0, p1, f0, f1, 0.69583512f, 0.69583512f);
+  ffma2(p0, p1, p0, p1, f0, f1, 0.99992492f, 0.99992492f);
+  r0 = __int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23));
+  r1 = __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23));
+}
+
 template <bool kPInTmem>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 flash_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
@@ -331,6 +368,342 @@ int launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, 
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Variant 2 ("shared S"): the S -> softmax -> PV -> S chain of one Q tile is cut.
+// In variants 0/1 S_q,j+1 may only be issued after PV_q,j has consumed P_q,j (P aliases S), so each Q tile runs
+// S(512 cyc) -> softmax(~1800) -> PV(512) strictly in series and the tensor pipe idles 36 % of the time (ncu, round 1:
+// the softmax warps spend 45 % of their samples waiting for S).  Here TMEM is laid out
+//     SA (128 cols, ONE S buffer shared by both Q tiles) | P0 (64) | P1 (64) | O0 (128) | O1 (128)   = 512 columns
+// A softmax warpgroup copies S into registers as soon as it is complete and releases SA at once (sa_free), so the
+// next S (of the other Q tile) is computed while both warpgroups are still busy with exp2; P_q lives in its own
+// columns, so PV_q,j never blocks an S.  S_q,j+1 is therefore ready long before softmax_q,j ends: the softmax warps
+// never wait for the tensor pipe and the two pipes (tensor, MUFU) overlap instead of alternating.
+// MMA issue order (one thread):  S0_0 S1_0 S0_1 | PV0_0 S1_1 PV1_0 S0_2 | PV0_1 S1_2 PV1_1 S0_3 | ...
+// K/V tiles are loaded in first-use order  K0 K1 V0 K2 V1 K3 V2 ...  (ring of 5 x 32 KB slots, freed in the same order).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int SA_NSLOT = 5;
+constexpr int SA_SMEM_BYTES = 2 * TILE_BYTES + SA_NSLOT * TILE_BYTES + 256 + 1024;
+
+// kTuned: PV_0,j is issued in two halves around S_1,j+1 (so the other Q tile's S does not queue behind a full PV),
+// the softmax row uses packed fp32x2 FMA/ADD, and kPoly of every 128 exponentials run on the FMA pipe (exp2_poly2).
+template <bool kTuned, int kPoly>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+flash_attn_sa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                     const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+  constexpr int NSLOT = SA_NSLOT;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;                    // 2 tiles
+  uint8_t* sKV = smem + 2 * TILE_BYTES;  // NSLOT tiles
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + NSLOT * TILE_BYTES);
+  uint64_t* q_full = bars;               // 1
+  uint64_t* kv_full = bars + 1;          // NSLOT
+  uint64_t* kv_empty = kv_full + NSLOT;  // NSLOT
+  uint64_t* s_full = kv_empty + NSLOT;   // 2  (MMA -> softmax q: S_q is in SA)
+  uint64_t* sa_free = s_full + 2;        // 1  (softmax -> MMA: SA copied to registers)
+  uint64_t* p_ready = sa_free + 1;       // 2  (softmax q -> MMA: P_q written)
+  uint64_t* pv_done = p_ready + 2;       // 2  (MMA -> softmax q: PV_q,j retired: P_q reusable, O_q idle)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int q_blk = blockIdx.x, head = blockIdx.y, batch = blockIdx.z;
+  const int nk = (p.Lk + BKV - 1) / BKV;
+
+  if (threadIdx.x == 0) {
+    vc::mbar_init(q_full, 1);
+    for (int i = 0; i < NSLOT; ++i) {
+      vc::mbar_init(&kv_full[i], 1);
+      vc::mbar_init(&kv_empty[i], 1);
+    }
+    vc::mbar_init(sa_free, 128);
+    for (int i = 0; i < 2; ++i) {
+      vc::mbar_init(&s_full[i], 1);
+      vc::mbar_init(&p_ready[i], 128);
+      vc::mbar_init(&pv_done[i], 1);
+    }
+    vc::fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    vc::tma_prefetch_desc(&tmQ);
+    vc::tma_prefetch_desc(&tmK);
+    vc::tma_prefetch_desc(&tmV);
+  }
+  if (warp == 2) vc::tmem_alloc(tmem_slot, 512);
+  vc::tc_fence_before();
+  __syncthreads();
+  vc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  constexpr uint32_t COL_SA = 0, COL_P = 128, COL_O = 256;
+
+  // position of a tile in the load / use / free sequence K0 K1 V0 K2 V1 K3 V2 ... K_{nk-1} V_{nk-2} V_{nk-1}
+  auto pos_k = [&](int j) { return j == 0 ? 0 : 2 * j - 1; };
+  auto pos_v = [&](int j) { return j == nk - 1 ? 2 * nk - 1 : 2 * j + 2; };
+
+  if (warp < 4) {
+    vc::reg_dealloc<56>();
+    if (warp == 0) {
+      // ---------------------------------------------------------------- TMA producer
+      if (vc::elect_one()) {
+        vc::mbar_expect_tx(q_full, 2 * TILE_BYTES);
+#pragma unroll
+        for (int qt = 0; qt < 2; ++qt)
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            vc::tma_load_4d(sQ + qt * TILE_BYTES + h * HALF_BYTES, &tmQ, q_full, h * 64, (q_blk * 2 + qt) * BQ, head,
+                            batch);
+        auto load = [&](int pos, const CUtensorMap* tm, int j) {
+          const int slot = pos % NSLOT;
+          const uint32_t ph = (pos / NSLOT) & 1;
+          vc::mbar_wait(&kv_empty[slot], ph ^ 1);
+          vc::mbar_expect_tx(&kv_full[slot], TILE_BYTES);
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            vc::tma_load_4d(sKV + slot * TILE_BYTES + h * HALF_BYTES, tm, &kv_full[slot], h * 64, j * BKV, head, batch);
+        };
+        load(0, &tmK, 0);
+        for (int j = 0; j < nk; ++j) {
+          if (j + 1 < nk) load(pos_k(j + 1), &tmK, j + 1);
+          load(pos_v(j), &tmV, j);
+        }
+      }
+    } else if (warp == 1) {
+      // ---------------------------------------------------------------- MMA issuer
+      if (vc::elect_one()) {
+        constexpr uint32_t idesc_s = vc::umma_idesc_bf16(BQ, BKV, 0, 0);  // Q (K-major) x K (K-major)
+        constexpr uint32_t idesc_o = vc::umma_idesc_bf16(BQ, HD, 0, 1);   // P (TMEM)    x V (MN-major)
+        auto kv_wait = [&](int pos) { vc::mbar_wait(&kv_full[pos % NSLOT], (pos / NSLOT) & 1); };
+        auto kv_addr = [&](int pos) { return vc::smem_u32(sKV + (pos % NSLOT) * TILE_BYTES); };
+        auto kv_release = [&](int pos) { vc::umma_commit(&kv_empty[pos % NSLOT]); };
+        uint32_t sa_uses = 0;  // completed sa_free phases consumed so far
+        auto wait_sa_free = [&]() {
+          vc::mbar_wait(sa_free, sa_uses & 1);
+          ++sa_uses;
+          vc::tc_fence_after();
+        };
+        auto issue_s = [&](int q, int j) {
+          const uint32_t qa = vc::smem_u32(sQ + q * TILE_BYTES);
+          const uint32_t ka = kv_addr(pos_k(j));
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k) {
+            const uint32_t off = (k >> 2) * HALF_BYTES + (k & 3) * 32;
+            vc::umma_ss(tmem_base + COL_SA, vc::umma_desc_sw128(qa + off, 16, 1024),
+                        vc::umma_desc_sw128(ka + off, 16, 1024), idesc_s, k != 0 ? 1u : 0u);
+          }
+          vc::umma_commit(&s_full[q]);
+        };
+        auto issue_pv_part = [&](int q, int j, int k0, int k1) {
+          const uint32_t va = kv_addr(pos_v(j));
+          const uint32_t d_tmem = tmem_base + COL_O + q * 128;
+          for (int k = k0; k < k1; ++k) {
+            const uint64_t vdesc = vc::umma_desc_sw128(va + k * 2048, HALF_BYTES, 1024);
+            vc::umma_ts(d_tmem, tmem_base + COL_P + q * 64 + k * 8, vdesc, idesc_o, (j != 0 || k != 0) ? 1u : 0u);
+          }
+          if (k1 == BKV / 16) vc::umma_commit(&pv_done[q]);
+        };
+        auto issue_pv = [&](int q, int j) { issue_pv_part(q, j, 0, BKV / 16); };
+        vc::mbar_wait(q_full, 0);
+        kv_wait(pos_k(0));
+        vc::tc_fence_after();
+        issue_s(0, 0);
+        wait_sa_free();
+        issue_s(1, 0);
+        kv_release(pos_k(0));
+        if (nk > 1) {
+          wait_sa_free();
+          kv_wait(pos_k(1));
+          vc::tc_fence_after();
+          issue_s(0, 1);
+        }
+        for (int j = 0; j < nk; ++j) {
+          vc::mbar_wait(&p_ready[0], j & 1);
+          kv_wait(pos_v(j));
+          vc::tc_fence_after();
+          if (kTuned && j + 1 < nk) {
+            issue_pv_part(0, j, 0, BKV / 32);
+            wait_sa_free();
+            issue_s(1, j + 1);
+            kv_release(pos_k(j + 1));
+            issue_pv_part(0, j, BKV / 32, BKV / 16);
+          } else {
+            issue_pv(0, j);
+            if (j + 1 < nk) {
+              wait_sa_free();
+              issue_s(1, j + 1);
+              kv_release(pos_k(j + 1));
+            }
+          }
+          vc::mbar_wait(&p_ready[1], j & 1);
+          vc::tc_fence_after();
+          if (kTuned && j + 2 < nk) {
+            issue_pv_part(1, j, 0, BKV / 32);
+            wait_sa_free();
+            kv_wait(pos_k(j + 2));
+            vc::tc_fence_after();
+            issue_s(0, j + 2);
+            issue_pv_part(1, j, BKV / 32, BKV / 16);
+            kv_release(pos_v(j));
+          } else {
+            issue_pv(1, j);
+            kv_release(pos_v(j));
+            if (j + 2 < nk) {
+              wait_sa_free();
+              kv_wait(pos_k(j + 2));
+              vc::tc_fence_after();
+              issue_s(0, j + 2);
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ softmax + correction + epilogue
+    vc::reg_alloc<208>();
+    const int q = (warp - 4) >> 2;        // Q tile of this warpgroup
+    const int quarter = warp & 3;         // TMEM lane quarter this warp may touch
+    const int row = quarter * 32 + lane;  // row inside the Q tile == TMEM lane
+    const uint32_t lane_bits = static_cast<uint32_t>(quarter * 32) << 16;
+    const uint32_t s_addr = tmem_base + COL_SA + lane_bits;
+    const uint32_t p_addr = tmem_base + COL_P + q * 64 + lane_bits;
+    const uint32_t o_addr = tmem_base + COL_O + q * 128 + lane_bits;
+    const float sl2 = p.scale_log2;
+    float m_run = -INFINITY;  // running (possibly stale) row max, raw score units
+    float l_run = 0.f;
+
+    for (int j = 0; j < nk; ++j) {
+      vc::mbar_wait(&s_full[q], j & 1);
+      vc::tc_fence_after();
+      uint32_t s[128];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) vc::tmem_ld32(s_addr + c * 32, s + c * 32);
+      vc::tmem_ld_wait();
+      vc::tc_fence_before();
+      vc::mbar_arrive(sa_free);  // SA may be overwritten by the other Q tile's S
+      if (j == nk - 1) {
+        const int valid = p.Lk - j * BKV;
+        if (valid < BKV) {
+#pragma unroll
+          for (int i = 0; i < 128; ++i)
+            if (i >= valid) s[i] = __float_as_uint(-INFINITY);
+        }
+      }
+      float mx[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) mx[i] = __uint_as_float(s[i]);
+#pragma unroll
+      for (int i = 8; i < 128; ++i) mx[i & 7] = fmaxf(mx[i & 7], __uint_as_float(s[i]));
+      const float mt = fmaxf(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])), fmaxf(fmaxf(mx[4], mx[5]), fmaxf(mx[6], mx[7])));
+      const float m_new = fmaxf(m_run, mt);
+      const bool need = (m_new - m_run) * sl2 > RESCALE_THRESHOLD;  // true on the first tile (m_run = -inf)
+      bool waited_pv = false;
+      if (__any_sync(0xffffffffu, need)) {
+        const float alpha = fast_exp2((m_run - m_new) * sl2);
+        l_run *= alpha;
+        m_run = m_new;
+        if (j > 0) {
+          vc::mbar_wait(&pv_done[q], (j - 1) & 1);  // O_q idle: PV_q,j-1 retired and PV_q,j waits for our p_ready
+          vc::tc_fence_after();
+          waited_pv = true;
+#pragma unroll 1
+          for (int c = 0; c < 4; ++c) {
+            uint32_t o[32];
+            vc::tmem_ld32(o_addr + c * 32, o);
+            vc::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            vc::tmem_st32(o_addr + c * 32, o);
+          }
+          vc::tmem_st_wait();
+        }
+      }
+      const float mb = m_run * sl2;
+      float sum = 0.f, sum1 = 0.f;
+      if (kTuned) {
+        float sum2 = 0.f, sum3 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+          float x0, x1, p0, p1;
+          ffma2(x0, x1, __uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1]), sl2, sl2, -mb, -mb);
+          if (kPoly > 0 && (i % (64 / (kPoly > 0 ? kPoly / 2 : 1))) == 1) {  // kPoly/2 pairs, evenly spread over the row
+            exp2_poly2(p0, p1, x0, x1);
+          } else {
+            p0 = fast_exp2(x0);
+            p1 = fast_exp2(x1);
+          }
+          if (i & 1) fadd2(sum2, sum3, sum2, sum3, p0, p1);
+          else fadd2(sum, sum1, sum, sum1, p0, p1);
+          s[i] = vc::pack_bf16x2(p0, p1);
+        }
+        l_run += (sum + sum1) + (sum2 + sum3);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+          const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -mb));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -mb));
+          sum += p0;
+          sum1 += p1;
+          s[i] = vc::pack_bf16x2(p0, p1);
+        }
+        l_run += sum + sum1;
+      }
+      if (j > 0 && !waited_pv) {
+        vc::mbar_wait(&pv_done[q], (j - 1) & 1);  // P_q,j-1 consumed
+        vc::tc_fence_after();
+      }
+      vc::tmem_st32(p_addr, s);
+      vc::tmem_st32(p_addr + 32, s + 32);
+      vc::tmem_st_wait();
+      vc::tc_fence_before();
+      vc::mbar_arrive(&p_ready[q]);
+    }
+
+    // epilogue: O_q / l -> bf16 -> global
+    vc::mbar_wait(&pv_done[q], (nk - 1) & 1);
+    vc::tc_fence_after();
+    const float inv_l = 1.0f / l_run;
+    const int q_row = (q_blk * 2 + q) * BQ + row;
+    __nv_bfloat16* orow = p.O + (long long)batch * p.o_stride_b + (long long)q_row * p.o_stride_l +
+                          (long long)head * p.o_stride_h;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t o[32];
+      vc::tmem_ld32(o_addr + c * 32, o);
+      vc::tmem_ld_wait();
+      if (q_row < p.Lq) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 u;
+          u.x = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 0]) * inv_l, __uint_as_float(o[g * 8 + 1]) * inv_l);
+          u.y = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 2]) * inv_l, __uint_as_float(o[g * 8 + 3]) * inv_l);
+          u.z = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 4]) * inv_l, __uint_as_float(o[g * 8 + 5]) * inv_l);
+          u.w = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 6]) * inv_l, __uint_as_float(o[g * 8 + 7]) * inv_l);
+          *reinterpret_cast<uint4*>(orow + c * 32 + g * 8) = u;
+        }
+      }
+    }
+  }
+
+  vc::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) vc::tmem_dealloc(tmem_base, 512);
+}
+
+template <bool kTuned, int kPoly>
+int launch_sa(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p, dim3 grid,
+              cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(flash_attn_sa_kernel<kTuned, kPoly>, cudaFuncAttributeMaxDynamicSharedMemorySize, SA_SMEM_BYTES);
+    if (e != cudaSuccess) {
+      vc_host::set_error("vc_flash_attn_fwd: cannot set %d B dynamic smem: %s", SA_SMEM_BYTES, cudaGetErrorString(e));
+      return (int)e;
+    }
+    attr_set = true;
+  }
+  flash_attn_sa_kernel<kTuned, kPoly><<<grid, NUM_THREADS, SA_SMEM_BYTES, s>>>(tq, tk, tv, p);
+  return 0;
+}
+
 }  // namespace
 
 // strides are in ELEMENTS: (batch, token, head); the head_dim axis must be contiguous (stride 1), head_dim == 128.
@@ -341,7 +714,7 @@ extern "C" int vc_flash_attn_fwd(const void* q, const void* k, const void* v, vo
   VC_CHECK_ARG(q && k && v && o && q_strides && k_strides && v_strides && o_strides, "vc_flash_attn_fwd: null pointer");
   VC_CHECK_ARG(head_dim == HD, "vc_flash_attn_fwd: head_dim %d unsupported (only 128)", head_dim);
   VC_CHECK_ARG(B > 0 && H > 0 && Lq >= 0 && Lk > 0, "vc_flash_attn_fwd: bad sizes B=%d H=%d Lq=%d Lk=%d", B, H, Lq, Lk);
-  VC_CHECK_ARG(variant == 0 || variant == 1, "vc_flash_attn_fwd: variant must be 0 (P in smem) or 1 (P in TMEM)");
+  VC_CHECK_ARG(variant >= 0 && variant <= 5, "vc_flash_attn_fwd: variant must be 0 (P in smem), 1 (P in TMEM over S) or 2 (shared S buffer)");
   const long long* all[4] = {q_strides, k_strides, v_strides, o_strides};
   for (int t = 0; t < 4; ++t)
     for (int i = 0; i < 3; ++i)
@@ -359,8 +732,15 @@ extern "C" int vc_flash_attn_fwd(const void* q, const void* k, const void* v, vo
   p.Lq = Lq; p.Lk = Lk;
   p.scale_log2 = softmax_scale * 1.4426950408889634f;
   dim3 grid((Lq + 2 * BQ - 1) / (2 * BQ), H, B);
-  rc = variant ? launch<true>(tq, tk, tv, p, grid, (cudaStream_t)stream)
-               : launch<false>(tq, tk, tv, p, grid, (cudaStream_t)stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (variant) {
+    case 0: rc = launch<false>(tq, tk, tv, p, grid, st); break;
+    case 1: rc = launch<true>(tq, tk, tv, p, grid, st); break;
+    case 2: rc = launch_sa<false, 0>(tq, tk, tv, p, grid, st); break;
+    case 3: rc = launch_sa<true, 0>(tq, tk, tv, p, grid, st); break;
+    case 4: rc = launch_sa<true, 16>(tq, tk, tv, p, grid, st); break;
+    default: rc = launch_sa<true, 32>(tq, tk, tv, p, grid, st); break;
+  }
   if (rc) return rc;
   VC_RETURN_LAUNCH_STATUS("vc_flash_attn_fwd");
 }

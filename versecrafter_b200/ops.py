@@ -182,7 +182,7 @@ def _strides3(t):
     return (ctypes.c_longlong * 3)(t.stride(0), t.stride(1), t.stride(2))
 
 
-def flash_attn(q, k, v, out=None, softmax_scale=None, variant=0):
+def flash_attn(q, k, v, out=None, softmax_scale=None, variant=4):
     """q [B, Lq, H, 128], k/v [B, Lk, H, 128] (arbitrary batch/token/head strides, unit stride on head_dim)
     -> out [B, Lq, H, 128]."""
     global launch_count

@@ -208,7 +208,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         self.num_inference_steps = None
         self.gradient_checkpointing = False
         self.sp_world_size, self.sp_world_rank, self.sp_group = 1, 0, None
-        self.attn_variant = int(os.environ.get("VC_ATTN_VARIANT", "1"))
+        self.attn_variant = int(os.environ.get("VC_ATTN_VARIANT", "4"))
         self._ws = {}
         self._rope_cache = {}
         self.record = None  # optional dict: tests set it to capture per-block tensors
