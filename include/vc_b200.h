@@ -75,6 +75,29 @@ int vc_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, int 
                       const long long* v_strides, const long long* o_strides, float softmax_scale, int variant,
                       void* stream);
 
+/* C1 — Ulysses sequence parallelism fused into the producer kernels (replaces the two all-to-alls that the
+ * reference gets from xfuser's SeqAllToAll4D inside videox_fun.dist.usp_attn_forward, bound at
+ * wan_transformer3d.py:906-921; source not in the reference tree).  The peer pointers are device addresses of the
+ * other GPUs' buffers mapped into this process (CUDA peer / symmetric memory); the kernels store straight into them
+ * over NVLink.  The caller orders the kernels across GPUs with a stream barrier (see versecrafter_b200/sp.py).
+ *
+ * vc_rmsnorm_rope_qkv_scatter: rows [q(D) | k(D) | v(D)] (row stride ld) of THIS rank's tokens -> q,k normalised and
+ *   rotated exactly as vc_rmsnorm_rope_qk, v copied, and head h of global token t of sample b stored at
+ *   peer_recv[h / heads_per_peer] + ((((which*n_batch + b)*l_total + t)*heads_per_peer + h % heads_per_peer)*head_dim,
+ *   which = 0,1,2 for q,k,v; n_batch = rows / rows_per_batch; t = pos_offset + row % rows_per_batch.
+ * vc_flash_attn_fwd_scatter: vc_flash_attn_fwd on the local heads over all tokens, with query row t stored at row
+ *   t % rows_per_peer of peer_o[t / rows_per_peer] (strides o_strides; the caller bakes its head offset into the
+ *   pointers).  variant >= 2. */
+int vc_rmsnorm_rope_qkv_scatter(const void* qkv, long long ld, long long rows, long long rows_per_batch,
+                                long long pos_offset, int D, const void* gain_q, const void* gain_k,
+                                const void* rope_table, int grid_f, int grid_h, int grid_w, int nf, int nh, int nw,
+                                float eps, void* const* peer_recv, int n_peers, int heads_per_peer, long long l_total,
+                                void* stream);
+int vc_flash_attn_fwd_scatter(const void* q, const void* k, const void* v, int B, int H, int Lq, int Lk, int head_dim,
+                              const long long* q_strides, const long long* k_strides, const long long* v_strides,
+                              void* const* peer_o, int n_peers, int rows_per_peer, const long long* o_strides,
+                              float softmax_scale, int variant, void* stream);
+
 /* K1/K2 front end — one sample [C, F, H, W] -> patch matrix A[L, 4C] (row stride ld_out), K ordered (c, ph, pw),
  * token n = (f*H/2 + h)*W/2 + w; Conv3d(kernel = stride = (1,2,2)) == vc_gemm_bf16(A, weight.view(D, 4C)) + bias
  * (wan_transformer3d.py:758-759, wan_transformer3d_versecrafter.py:199-201, :262-263, :340-343). */

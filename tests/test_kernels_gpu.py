@@ -233,6 +233,40 @@ def test_flash_attn_large_scores_rescale(ops):
         assert relerr(ops.flash_attn(q, k, v, variant=variant), restate.sdpa(q, k, v)) < 1e-2, variant
 
 
+@pytest.mark.parametrize("P", [2, 4, 8])
+def test_ulysses_fused_kernels_emulated_ranks(ops, P):
+    """The fused Ulysses kernels with the P ranks emulated on ONE GPU (the "peer" buffers are P local tensors): the
+    head-scatter inside RMSNorm+RoPE and the token-scatter inside the attention epilogue must reproduce, bit for bit,
+    the un-sharded kernels' results sliced the way the all-to-alls would slice them."""
+    B, H, d, grid = 2, 16, 128, (2, 8, 24)
+    D, L = H * d, grid[0] * grid[1] * grid[2]
+    Lp, Hp = L // P, H // P
+    full = _rand((B, L, 3 * D), 40)
+    gq = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    gk = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    rope = ops.rope_table(d, grid, "cuda")
+    # un-sharded reference through the plain kernels
+    ref = full.reshape(B * L, 3 * D).clone()
+    ops.rmsnorm_rope_(ref, D, 2, gq, gk, L, rope=rope, grid=grid)
+    q_ref, k_ref, v_ref = (ref[:, i * D:(i + 1) * D].view(B, L, H, d) for i in range(3))
+    o_ref = ops.flash_attn(q_ref, k_ref, v_ref, variant=4)
+    # emulated ranks
+    recv = [torch.full((3, B, L, Hp, d), float("nan"), device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    attn = [torch.full((B, Lp, H, d), float("nan"), device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    for r in range(P):
+        mine = full[:, r * Lp:(r + 1) * Lp].reshape(B * Lp, 3 * D).contiguous()
+        ops.rmsnorm_rope_qkv_scatter(mine, D, gq, gk, Lp, [t.data_ptr() for t in recv], Hp, L, rope, grid,
+                                     pos_offset=r * Lp)
+    for p in range(P):
+        for i, want in enumerate((q_ref, k_ref, v_ref)):
+            assert torch.equal(recv[p][i], want[:, :, p * Hp:(p + 1) * Hp]), (p, i)
+    for p in range(P):
+        ops.flash_attn_scatter(recv[p][0], recv[p][1], recv[p][2], [t.data_ptr() + p * Hp * d * 2 for t in attn], Lp,
+                               (Lp * D, D, d), variant=4)
+    for r in range(P):
+        assert torch.equal(attn[r], o_ref[:, r * Lp:(r + 1) * Lp]), r
+
+
 def test_patchify_unpatchify(ops):
     u = _rand((12, 3, 8, 10), 28)
     got = ops.patchify(u)

@@ -47,6 +47,34 @@ def test_ulysses_layouts_world2():
     assert dict(ret) == {0: "ok", 1: "ok"}, dict(ret)
 
 
+def test_fused_scatter_layouts_equal_all_to_all_slices():
+    """The destination formulas of the fused kernels (sp.recv_layout_index / attn_layout_index, mirrored in
+    norm_kernels.cu / flash_attn_tcgen05.cu) place every element exactly where scatter_heads / gather_heads would."""
+    from versecrafter_b200 import sp
+    B, L, H, d, P = 2, 12, 8, 4, 4
+    Lp, Hp = L // P, H // P
+    g = torch.Generator().manual_seed(1)
+    qkv = torch.randn(3, B, L, H, d, generator=g)
+    recv = [torch.full((3 * B * L * Hp * d,), float("nan")) for _ in range(P)]
+    for w in range(3):
+        for b in range(B):
+            for t in range(L):
+                for h in range(H):
+                    peer, off = sp.recv_layout_index(w, b, t, h, B, L, Hp, d)
+                    recv[peer][off:off + d] = qkv[w, b, t, h]
+    for p in range(P):
+        assert torch.equal(recv[p].view(3, B, L, Hp, d), qkv[:, :, :, p * Hp:(p + 1) * Hp])
+    o = torch.randn(B, L, H, d, generator=g)   # attention output, produced per rank as [B, L, Hp, d]
+    attn = [torch.full((B * Lp * H * d,), float("nan")) for _ in range(P)]
+    for b in range(B):
+        for t in range(L):
+            for h in range(H):
+                peer, off = sp.attn_layout_index(b, t, h, Lp, H, d)
+                attn[peer][off:off + d] = o[b, t, h]
+    for r in range(P):
+        assert torch.equal(attn[r].view(B, Lp, H, d), o[:, r * Lp:(r + 1) * Lp])
+
+
 def test_bench_work_formula_matches_survey():
     import bench
     cfg, grid, _ = bench.CONFIGS["c3"]

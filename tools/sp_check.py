@@ -26,17 +26,25 @@ def main():
     L = grid[0] * grid[1] * grid[2] // 4
     y1 = model(x, t, geo, ctx, L).float()
     model.enable_multi_gpus_inference()
-    yp = model(x, t, geo, ctx, L).float()
-    torch.cuda.synchronize()
-    cos = float(torch.nn.functional.cosine_similarity(y1.flatten().double(), yp.flatten().double(), dim=0))
-    rel = float((y1 - yp).norm() / y1.norm())
-    ok = cos > 0.9999 and rel < 1e-2
-    flags = torch.tensor([1.0 if ok else 0.0], device="cuda")
-    dist.all_reduce(flags, op=dist.ReduceOp.MIN)
-    if rank == 0:
-        print(f"sp_check world={world}: cosine {cos:.7f} rel-L2 {rel:.5f} -> {'OK' if flags.item() == 1 else 'FAIL'}", flush=True)
+    all_ok = True
+    for mode in ("nccl", "fused"):  # NCCL all_to_all path, then the peer-memory path fused into the kernels
+        os.environ["VC_SP_MODE"] = mode
+        model._px, model._px_failed = None, False
+        yp = model(x, t, geo, ctx, L).float()
+        yp2 = model(x, t, geo, ctx, L).float()  # second call: buffers are reused across steps
+        torch.cuda.synchronize()
+        used = "fused" if model._px is not None else "nccl"
+        cos = float(torch.nn.functional.cosine_similarity(y1.flatten().double(), yp.flatten().double(), dim=0))
+        rel = float((y1 - yp).norm() / y1.norm())
+        ok = cos > 0.9999 and rel < 1e-2 and torch.equal(yp, yp2) and used == mode
+        flags = torch.tensor([1.0 if ok else 0.0], device="cuda")
+        dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+        all_ok = all_ok and flags.item() == 1
+        if rank == 0:
+            print(f"sp_check world={world} mode={mode} (ran {used}): cosine {cos:.7f} rel-L2 {rel:.5f} "
+                  f"repeatable={torch.equal(yp, yp2)} -> {'OK' if flags.item() == 1 else 'FAIL'}", flush=True)
     dist.destroy_process_group()
-    sys.exit(0 if flags.item() == 1 else 1)
+    sys.exit(0 if all_ok else 1)
 
 
 if __name__ == "__main__":

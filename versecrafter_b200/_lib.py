@@ -11,6 +11,7 @@ _vp = ctypes.c_void_p
 _i = ctypes.c_int
 _f = ctypes.c_float
 _llp = ctypes.POINTER(ctypes.c_longlong)
+_vpp = ctypes.POINTER(ctypes.c_void_p)
 
 SIGNATURES = {
     "vc_version": (_i, []),
@@ -21,6 +22,10 @@ SIGNATURES = {
     "vc_rmsnorm_rope_qk": (_i, [_vp, _c_ll, _c_ll, _c_ll, _c_ll, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "vc_gemm_bf16": (_i, [_vp, _c_ll, _vp, _c_ll, _vp, _c_ll, _c_ll, _c_ll, _c_ll, _i, _vp, _vp, _c_ll, _c_ll, _vp, _c_ll, _f, _vp]),
     "vc_flash_attn_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _llp, _llp, _llp, _llp, _f, _i, _vp]),
+    "vc_rmsnorm_rope_qkv_scatter": (_i, [_vp, _c_ll, _c_ll, _c_ll, _c_ll, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f,
+                                         _vpp, _i, _i, _c_ll, _vp]),
+    "vc_flash_attn_fwd_scatter": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _llp, _llp, _llp, _vpp, _i, _i, _llp, _f, _i,
+                                       _vp]),
     "vc_patchify": (_i, [_vp, _vp, _i, _i, _i, _i, _c_ll, _vp]),
     "vc_unpatchify": (_i, [_vp, _c_ll, _vp, _i, _i, _i, _i, _vp]),
 }

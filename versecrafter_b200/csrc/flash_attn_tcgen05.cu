@@ -38,6 +38,11 @@ struct AttnParams {
   long long o_stride_b, o_stride_l, o_stride_h;  // elements
   int Lq, Lk;
   float scale_log2;  // softmax_scale * log2(e)
+  // Ulysses output scatter (variants >= 2): query row t belongs to peer t / rows_per_peer and is stored at row
+  // t % rows_per_peer of o_peer[that peer] (same strides as O).  n_peers == 0: plain store to O.
+  __nv_bfloat16* o_peer[8];
+  int n_peers;
+  int rows_per_peer;
 };
 
 __device__ __forceinline__ float fast_exp2(float x) {
@@ -662,7 +667,14 @@ flash_attn_sa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     vc::tc_fence_after();
     const float inv_l = 1.0f / l_run;
     const int q_row = (q_blk * 2 + q) * BQ + row;
-    __nv_bfloat16* orow = p.O + (long long)batch * p.o_stride_b + (long long)q_row * p.o_stride_l +
+    __nv_bfloat16* obase = p.O;
+    int o_row = q_row;
+    if (p.n_peers > 0 && q_row < p.Lq) {  // inverse all-to-all fused into the epilogue: store into the owner's buffer
+      const int owner = q_row / p.rows_per_peer;
+      obase = p.o_peer[owner];
+      o_row = q_row - owner * p.rows_per_peer;
+    }
+    __nv_bfloat16* orow = obase + (long long)batch * p.o_stride_b + (long long)o_row * p.o_stride_l +
                           (long long)head * p.o_stride_h;
 #pragma unroll 1
     for (int c = 0; c < 4; ++c) {
@@ -707,10 +719,10 @@ int launch_sa(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& t
 }  // namespace
 
 // strides are in ELEMENTS: (batch, token, head); the head_dim axis must be contiguous (stride 1), head_dim == 128.
-extern "C" int vc_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, int B, int H, int Lq, int Lk,
-                                 int head_dim, const long long* q_strides, const long long* k_strides,
-                                 const long long* v_strides, const long long* o_strides, float softmax_scale,
-                                 int variant, void* stream) {
+static int attn_impl(const void* q, const void* k, const void* v, void* o, int B, int H, int Lq, int Lk, int head_dim,
+                     const long long* q_strides, const long long* k_strides, const long long* v_strides,
+                     const long long* o_strides, float softmax_scale, int variant, void* const* peer_o, int n_peers,
+                     int rows_per_peer, void* stream) {
   VC_CHECK_ARG(q && k && v && o && q_strides && k_strides && v_strides && o_strides, "vc_flash_attn_fwd: null pointer");
   VC_CHECK_ARG(head_dim == HD, "vc_flash_attn_fwd: head_dim %d unsupported (only 128)", head_dim);
   VC_CHECK_ARG(B > 0 && H > 0 && Lq >= 0 && Lk > 0, "vc_flash_attn_fwd: bad sizes B=%d H=%d Lq=%d Lk=%d", B, H, Lq, Lk);
@@ -731,6 +743,9 @@ extern "C" int vc_flash_attn_fwd(const void* q, const void* k, const void* v, vo
   p.o_stride_b = o_strides[0]; p.o_stride_l = o_strides[1]; p.o_stride_h = o_strides[2];
   p.Lq = Lq; p.Lk = Lk;
   p.scale_log2 = softmax_scale * 1.4426950408889634f;
+  p.n_peers = n_peers;
+  p.rows_per_peer = rows_per_peer > 0 ? rows_per_peer : 1;
+  for (int i = 0; i < 8; ++i) p.o_peer[i] = (__nv_bfloat16*)(i < n_peers ? peer_o[i] : nullptr);
   dim3 grid((Lq + 2 * BQ - 1) / (2 * BQ), H, B);
   cudaStream_t st = (cudaStream_t)stream;
   switch (variant) {
@@ -743,4 +758,27 @@ extern "C" int vc_flash_attn_fwd(const void* q, const void* k, const void* v, vo
   }
   if (rc) return rc;
   VC_RETURN_LAUNCH_STATUS("vc_flash_attn_fwd");
+}
+
+extern "C" int vc_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, int B, int H, int Lq, int Lk,
+                                 int head_dim, const long long* q_strides, const long long* k_strides,
+                                 const long long* v_strides, const long long* o_strides, float softmax_scale,
+                                 int variant, void* stream) {
+  return attn_impl(q, k, v, o, B, H, Lq, Lk, head_dim, q_strides, k_strides, v_strides, o_strides, softmax_scale, variant,
+                   nullptr, 0, 0, stream);
+}
+
+extern "C" int vc_flash_attn_fwd_scatter(const void* q, const void* k, const void* v, int B, int H, int Lq, int Lk,
+                                         int head_dim, const long long* q_strides, const long long* k_strides,
+                                         const long long* v_strides, void* const* peer_o, int n_peers,
+                                         int rows_per_peer, const long long* o_strides, float softmax_scale,
+                                         int variant, void* stream) {
+  VC_CHECK_ARG(peer_o && n_peers >= 1 && n_peers <= 8, "vc_flash_attn_fwd_scatter: n_peers must be in 1..8");
+  VC_CHECK_ARG(variant >= 2, "vc_flash_attn_fwd_scatter: needs a shared-S variant (>= 2)");
+  VC_CHECK_ARG(rows_per_peer > 0 && (long long)rows_per_peer * n_peers >= Lq,
+               "vc_flash_attn_fwd_scatter: rows_per_peer * n_peers must cover Lq");
+  for (int i = 0; i < n_peers; ++i)
+    VC_CHECK_ARG(peer_o[i] && (uintptr_t)peer_o[i] % 16 == 0, "vc_flash_attn_fwd_scatter: bad peer pointer %d", i);
+  return attn_impl(q, k, v, peer_o[0], B, H, Lq, Lk, head_dim, q_strides, k_strides, v_strides, o_strides, softmax_scale,
+                   variant, peer_o, n_peers, rows_per_peer, stream);
 }

@@ -364,6 +364,109 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_block_k
 }
 
 // ----------------------------------------------------------------------------------------------------
+// Ulysses producer: RMSNorm + RoPE of q and k (as above) and a pass-through of v, with the
+// result STORED DIRECTLY INTO THE RECEIVE BUFFERS OF THE PEER GPUs over NVLink (peer-mapped pointers) instead of
+// in place: rank p receives heads [p*Hp, (p+1)*Hp) of every token.  Destination layout at each peer:
+//   recv[which(q,k,v)][b][global token][local head][head_dim]      (bf16)
+// so the all-to-all "scatter heads / gather sequence" of the reference's usp_attn_forward (xfuser SeqAllToAll4D,
+// not in the reference tree) happens inside this kernel's epilogue: no send-layout copy, no NCCL call, no
+// receive-layout copy.  A cross-GPU barrier on the stream (host side) orders it against the attention kernel.
+// ----------------------------------------------------------------------------------------------------
+struct PeerPtrs {
+  __nv_bfloat16* p[8];
+};
+
+template <int VPT>
+__global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_scatter_kernel(
+    const __nv_bfloat16* __restrict__ qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset,
+    int D, const __nv_bfloat16* __restrict__ gq, const __nv_bfloat16* __restrict__ gk, const float2* __restrict__ tab,
+    int Fg, int Hg, int Wg, int nf, int nh, int nw, float eps, PeerPtrs peers, int heads_per_peer, long long l_total,
+    int n_batch) {
+  __shared__ float red[3][ROW_NT / 32];
+  const int nvec = D >> 3;
+  const float inv_d = 1.0f / (float)D;
+  const int half_d = nf + nh + nw;
+  const int vec_per_head = half_d >> 2;  // head_dim / 8
+  const float2* tab_f = tab;
+  const float2* tab_h = tab + (long long)Fg * nf;
+  const float2* tab_w = tab_h + (long long)Hg * nh;
+  const int j0 = ((threadIdx.x * 8) % (2 * half_d)) >> 1;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const long long b = row / rows_per_batch;
+    const long long pos = pos_offset + (row - b * rows_per_batch);
+    const bool rot = pos < (long long)Fg * Hg * Wg;
+    float2 cs[4];
+    if (rot) {
+      const int pw = (int)(pos % Wg);
+      const int ph = (int)((pos / Wg) % Hg);
+      const int pf = (int)(pos / ((long long)Wg * Hg));
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const int j = j0 + p;
+        if (j < nf) cs[p] = __ldg(tab_f + pf * nf + j);
+        else if (j < nf + nh) cs[p] = __ldg(tab_h + ph * nh + (j - nf));
+        else cs[p] = __ldg(tab_w + pw * nw + (j - nf - nh));
+      }
+    }
+#pragma unroll 1
+    for (int which = 0; which < 3; ++which) {
+      const uint4* xr = reinterpret_cast<const uint4*>(qkv + row * ld + (long long)which * D);
+      const uint4* gr = reinterpret_cast<const uint4*>(which == 0 ? gq : gk);
+      // element offset of (which, b, pos, local head 0, 0) inside a peer's receive buffer
+      const long long dst_row = (((long long)which * n_batch + b) * l_total + pos) * heads_per_peer;
+      uint4 raw[VPT];
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + ROW_NT * i;
+        raw[i] = (v < nvec) ? ld_stream(xr + v) : make_uint4(0, 0, 0, 0);
+      }
+      float r = 1.f;
+      if (which < 2) {
+        float ss = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+          float f[8];
+          unpack8(raw[i], f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) ss = fmaf(f[j], f[j], ss);
+        }
+        r = bf16_round(rsqrtf(block_sum(ss, red[which]) * inv_d + eps));
+      } else {
+        __syncthreads();  // red[0] / red[1] are rewritten by the next row only after everybody read them
+      }
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + ROW_NT * i;
+        if (v < nvec) {
+          uint4 outv = raw[i];
+          if (which < 2) {
+            float f[8], g[8];
+            unpack8(raw[i], f);
+            unpack8(__ldg(gr + v), g);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = bf16_round(bf16_round(f[j] * r) * g[j]);
+            if (rot) {
+#pragma unroll
+              for (int p = 0; p < 4; ++p) {
+                const float a = f[2 * p], c = f[2 * p + 1];
+                f[2 * p] = a * cs[p].x - c * cs[p].y;
+                f[2 * p + 1] = a * cs[p].y + c * cs[p].x;
+              }
+            }
+            outv = pack8(f);
+          }
+          const int head = v / vec_per_head;
+          const int peer = head / heads_per_peer;
+          const int hl = head - peer * heads_per_peer;
+          __nv_bfloat16* dst = peers.p[peer] + ((dst_row + hl) * vec_per_head + (v - head * vec_per_head)) * 8;
+          *reinterpret_cast<uint4*>(dst) = outv;
+        }
+      }
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------
 // patchify: [C, F, H, W] bf16 (one sample) -> A[L, C*4] bf16, K ordered (c, ph, pw)  (SURVEY App. A.1).
 // Feeds the tcgen05 GEMM that implements the Conv3d patch embedding (stride == kernel, so it is a pure GEMM).
 // thread -> (token, c): reads two 4-byte pairs (rows 2h, 2h+1), writes 8 contiguous bytes.
@@ -510,6 +613,38 @@ int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_p
   });
   VC_CHECK_ARG(rc == 0, "vc_rmsnorm_rope_qk: unsupported D=%d", D);
   VC_RETURN_LAUNCH_STATUS("vc_rmsnorm_rope_qk");
+}
+
+int vc_rmsnorm_rope_qkv_scatter(const void* qkv, long long ld, long long rows, long long rows_per_batch,
+                                long long pos_offset, int D, const void* gain_q, const void* gain_k,
+                                const void* rope_table, int grid_f, int grid_h, int grid_w, int nf, int nh, int nw,
+                                float eps, void* const* peer_recv, int n_peers, int heads_per_peer, long long l_total,
+                                void* stream) {
+  VC_CHECK_ARG(qkv && gain_q && gain_k && rope_table && peer_recv, "vc_rmsnorm_rope_qkv_scatter: null pointer");
+  VC_CHECK_ARG(n_peers >= 1 && n_peers <= 8, "vc_rmsnorm_rope_qkv_scatter: n_peers=%d must be in 1..8", n_peers);
+  VC_CHECK_ARG(nf > 0 && nh > 0 && nw > 0 && (nf + nh + nw) % 4 == 0, "vc_rmsnorm_rope_qkv_scatter: bad rope split");
+  const int hd = 2 * (nf + nh + nw);
+  VC_CHECK_ARG(D % hd == 0 && (ROW_NT * 8) % hd == 0 && D <= 8192 && ld % 8 == 0 && ld >= 3LL * D,
+               "vc_rmsnorm_rope_qkv_scatter: unsupported D=%d / head_dim=%d / ld", D, hd);
+  VC_CHECK_ARG(heads_per_peer > 0 && (long long)heads_per_peer * n_peers == D / hd,
+               "vc_rmsnorm_rope_qkv_scatter: heads_per_peer * n_peers must equal the head count");
+  VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && rows % rows_per_batch == 0 && pos_offset >= 0 &&
+                   pos_offset + rows_per_batch <= l_total,
+               "vc_rmsnorm_rope_qkv_scatter: bad rows / positions");
+  if (rows == 0) return 0;
+  PeerPtrs pp;
+  for (int i = 0; i < 8; ++i) pp.p[i] = (__nv_bfloat16*)(i < n_peers ? peer_recv[i] : nullptr);
+  for (int i = 0; i < n_peers; ++i) VC_CHECK_ARG(pp.p[i] && (uintptr_t)pp.p[i] % 16 == 0, "vc_rmsnorm_rope_qkv_scatter: bad peer pointer %d", i);
+  int rc = dispatch_vpt(D, [&](auto vpt) {
+    constexpr int V = decltype(vpt)::value;
+    rmsnorm_rope_scatter_kernel<V><<<grid_for_block_rows(rows), ROW_NT, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)qkv, ld, rows, rows_per_batch, pos_offset, D, (const __nv_bfloat16*)gain_q,
+        (const __nv_bfloat16*)gain_k, (const float2*)rope_table, grid_f, grid_h, grid_w, nf, nh, nw, eps, pp,
+        heads_per_peer, l_total, (int)(rows / rows_per_batch));
+    return 0;
+  });
+  VC_CHECK_ARG(rc == 0, "vc_rmsnorm_rope_qkv_scatter: unsupported D=%d", D);
+  VC_RETURN_LAUNCH_STATUS("vc_rmsnorm_rope_qkv_scatter");
 }
 
 int vc_patchify(const void* in, void* out, int C, int F, int H, int W, long long ld_out, void* stream) {

@@ -206,6 +206,49 @@ def flash_attn(q, k, v, out=None, softmax_scale=None, variant=4):
     return out
 
 
+def _ptr_array(ptrs):
+    return (ctypes.c_void_p * len(ptrs))(*[int(x) for x in ptrs])
+
+
+def rmsnorm_rope_qkv_scatter(qkv, D, gain_q, gain_k, rows_per_batch, peer_ptrs, heads_per_peer, l_total, rope, grid,
+                             pos_offset=0, eps=1e-6):
+    """qkv [rows, 3D] of this rank's tokens -> RMSNorm+RoPE(q,k), v, written head-scattered into the peers' receive
+    buffers (device addresses `peer_ptrs`, layout [3, B, l_total, heads_per_peer, d])."""
+    global launch_count
+    _chk(qkv, "qkv"); _chk(gain_q, "gain_q"); _chk(gain_k, "gain_k")
+    assert qkv.dim() == 2 and qkv.shape[1] >= 3 * D
+    rows, ld = qkv.shape[0], qkv.stride(0)
+    table, (nf, nh, nw) = rope
+    gf, gh, gw = grid
+    lib = _lib.load()
+    with _timed("rmsnorm_rope", 6.0 * rows * D):
+        _lib.check(lib.vc_rmsnorm_rope_qkv_scatter(_ptr(qkv), ld, rows, rows_per_batch, pos_offset, D, _ptr(gain_q),
+                                                   _ptr(gain_k), _ptr(table), gf, gh, gw, nf, nh, nw, eps,
+                                                   _ptr_array(peer_ptrs), len(peer_ptrs), heads_per_peer, l_total,
+                                                   _stream()), "vc_rmsnorm_rope_qkv_scatter")
+    launch_count += 1
+
+
+def flash_attn_scatter(q, k, v, peer_ptrs, rows_per_peer, o_strides, softmax_scale=None, variant=4):
+    """q,k,v [B, L, Hp, 128] (local heads, all tokens); output row t -> row t % rows_per_peer of peer t // rows_per_peer
+    (device addresses `peer_ptrs`, element strides o_strides = (batch, token, head))."""
+    global launch_count
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _chk(t, n)
+        assert t.dim() == 4 and t.shape[-1] == 128, (n, t.shape)
+    B, Lq, H, d = q.shape
+    Lk = k.shape[1]
+    if softmax_scale is None:
+        softmax_scale = 1.0 / math.sqrt(d)
+    lib = _lib.load()
+    with _timed("attn_self" if Lk > 1024 else "attn_cross", 4.0 * B * H * Lq * Lk * d):
+        _lib.check(lib.vc_flash_attn_fwd_scatter(_ptr(q), _ptr(k), _ptr(v), B, H, Lq, Lk, d, _strides3(q), _strides3(k),
+                                                 _strides3(v), _ptr_array(peer_ptrs), len(peer_ptrs), rows_per_peer,
+                                                 (ctypes.c_longlong * 3)(*o_strides), float(softmax_scale), int(variant),
+                                                 _stream()), "vc_flash_attn_fwd_scatter")
+    launch_count += 1
+
+
 def patchify(u, out=None):
     """u [C, F, H, W] bf16 -> [L, 4C]."""
     global launch_count

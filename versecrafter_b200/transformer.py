@@ -208,6 +208,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         self.num_inference_steps = None
         self.gradient_checkpointing = False
         self.sp_world_size, self.sp_world_rank, self.sp_group = 1, 0, None
+        self._px, self._px_failed = None, False
         self.attn_variant = int(os.environ.get("VC_ATTN_VARIANT", "4"))
         self._ws = {}
         self._rope_cache = {}
@@ -321,6 +322,22 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         self.sp_world_rank = dist.get_rank(group)
         if self.num_heads % self.sp_world_size:
             raise VCError(f"{self.num_heads} heads do not split over {self.sp_world_size} ranks")
+
+    def _peer_exchange(self):
+        """Symmetric-memory exchange for the fused Ulysses path; None -> NCCL all_to_all path (VC_SP_MODE=nccl, or
+        symmetric memory unavailable on this system — reported once, never silently)."""
+        if self._px is None and not self._px_failed:
+            if os.environ.get("VC_SP_MODE", "fused") == "nccl":
+                self._px_failed = True
+            else:
+                try:
+                    self._px = sp.PeerExchange(self.sp_group, self.device)
+                    self._px.buffer("attn_recv", 1024)  # first rendezvous: fails here if peer mapping is unsupported
+                except Exception as e:  # noqa: BLE001
+                    self._px, self._px_failed = None, True
+                    if self.sp_world_rank == 0:
+                        print(f"[versecrafter_b200] symmetric memory unavailable ({e!r}); using NCCL all_to_all", flush=True)
+        return self._px
 
     def all_gather(self, x, dim=1):
         return sp.all_gather_tokens(x, dim, self.sp_group)
@@ -453,9 +470,16 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         # self-attention half
         ops.ln_modulate(x2d, m[:, 0], m[:, 1], Lp, eps=self.eps, out=h)
         qkv = ops.gemm(h, pk["wqkv"], pk["bqkv"], out=self._buf("qkv", (rows, 3 * D)))
+        attn = self._buf("attn", (rows, D))
+        if self.sp_world_size > 1 and self._peer_exchange() is not None:
+            # Ulysses with both all-to-alls fused into the producer kernels' stores over NVLink (sp.py)
+            attn_sa = sp.ulysses_attention_fused(self._px, qkv, B, Lp, H, self.d, sa.norm_q.weight, sa.norm_k.weight,
+                                                 st.rope, st.grid, self.eps, max(self.attn_variant, 2))
+            ops.gemm(attn_sa, sa.o.weight, sa.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_GATE | ops.EPI_RES, gate=m[:, 2],
+                     rows_per_batch=Lp, residual=x2d, out=x2d)
+            return self._block_tail(blk, x2d, m, ctx, st, h, attn)
         ops.rmsnorm_rope_(qkv, D, 2, sa.norm_q.weight, sa.norm_k.weight, Lp, eps=self.eps, rope=st.rope, grid=st.grid,
                           pos_offset=self.sp_world_rank * Lp)
-        attn = self._buf("attn", (rows, D))
         if self.sp_world_size == 1:
             q4, k4, v4 = (qkv[:, i * D:(i + 1) * D].view(B, Lp, H, self.d) for i in range(3))
             if st.k_len < Lp:  # padded tokens are masked as keys (k_lens=seq_lens, :394-399)
@@ -466,6 +490,14 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
                                  variant=self.attn_variant)
         ops.gemm(attn, sa.o.weight, sa.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_GATE | ops.EPI_RES, gate=m[:, 2],
                  rows_per_batch=Lp, residual=x2d, out=x2d)
+        return self._block_tail(blk, x2d, m, ctx, st, h, attn)
+
+    def _block_tail(self, blk, x2d, m, ctx, st, h, attn):
+        """cross-attention + FFN halves of the block (token-local under sequence parallelism)."""
+        B, Lp, D, H = st.B, st.Lp, self.dim, self.num_heads
+        rows = B * Lp
+        pk = blk.ensure_packed()
+        ca = blk.cross_attn
         # cross-attention
         ops.ln_affine(x2d, blk.norm3.weight, blk.norm3.bias, eps=self.eps, out=h)
         qc = ops.gemm(h, ca.q.weight, ca.q.bias, out=self._buf("qc", (rows, D)))
