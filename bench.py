@@ -114,43 +114,64 @@ def make_inputs(cfg, grid, B=2):
 # ------------------------------------------------------------------------------------------------------------------
 # CPU arm: the oracle's port of the reference path, timed on the host cores on a bounded sample
 # ------------------------------------------------------------------------------------------------------------------
-def cpu_reference_sample(cfg_name, steps=1, warmup=0, seconds_budget=25.0):
+def _block_flops(cfg, Ls, T=512):
+    D, Fd = cfg["dim"], cfg["ffn_dim"]
+    return 12.0 * Ls * D * D + 4.0 * T * D * D + 4.0 * Ls * D * Fd + 4.0 * Ls * Ls * D + 4.0 * Ls * T * D
+
+
+def cpu_reference_sample(cfg_name, steps=1, warmup=0, seconds_budget=28.0):
     """One DiT block (the reference's WanAttentionBlock.forward restated in oracle/restate.py) at the config's real
-    width, fp32, on a token sample sized to the time budget; tokens/s is extrapolated to a full step by the block count
-    (optimistic for the CPU: attention is quadratic in L and the sample is short)."""
+    width and real H'xW' token grid, fp32, on all host cores.  The number of latent frames of the sample is chosen from
+    a 1-frame calibration run so that one block takes about `seconds_budget` seconds (the full 21 frames when the box
+    is fast enough); tokens/s of a whole step = sample tokens / (seconds per block * number of blocks)."""
     from oracle import restate
     cfg, grid, _ = CONFIGS[cfg_name]
     cores = len(os.sched_getaffinity(0))
     torch.set_num_threads(cores)
     D, H = cfg["dim"], cfg["num_heads"]
-    sgrid = (2, 16, 32) if D >= 1536 else (5, 15, 26)   # 1024 / 1950 tokens
-    Ls = sgrid[0] * sgrid[1] * sgrid[2]
-    one = dict(cfg, num_layers=1)
+    gh, gw = grid[1] // 2, grid[2] // 2
     shapes = restate.block_param_shapes(D, cfg["ffn_dim"])
     g = torch.Generator().manual_seed(0)
     sd = {"b." + k: (torch.randn(s, generator=g) * (0.02 if len(s) > 1 else 0.1) + (1.0 if "norm" in k and k.endswith("weight") else 0.0))
           for k, s in shapes.items()}
-    x = torch.randn(1, Ls, D, generator=g)
     e0 = torch.randn(1, 6, D, generator=g) * 0.1
     ctx = torch.randn(1, 512, D, generator=g)
-    ang = restate.rope_angles(D // H, sgrid)
-    times = []
-    with torch.no_grad():
-        for i in range(warmup + steps):
-            t0 = time.perf_counter()
+
+    def run_block(frames):
+        sgrid = (frames, gh, gw)
+        Ls = frames * gh * gw
+        x = torch.randn(1, Ls, D, generator=g)
+        ang = restate.rope_angles(D // H, sgrid)
+        t0 = time.perf_counter()
+        with torch.no_grad():
             restate.dit_block(sd, "b.", x, e0, ang, ctx, H)
-            dt = time.perf_counter() - t0
-            if i >= warmup:
-                times.append(dt)
-            if sum(times) > seconds_budget and times:
-                break
+        return time.perf_counter() - t0, Ls, sgrid
+
+    run_block(1)                                  # page in / thread pool
+    t_cal, L_cal, _ = run_block(1)
+    rate = _block_flops(cfg, L_cal) / t_cal       # flop/s of this box on the 1-frame block
+    frames = 1
+    for f in range(grid[0], 0, -1):
+        if _block_flops(cfg, f * gh * gw) / rate <= seconds_budget:
+            frames = f
+            break
+    times = []
+    for i in range(warmup + steps):
+        dt, Ls, sgrid = run_block(frames)
+        if i >= warmup:
+            times.append(dt)
+        if sum(times) > 2.5 * seconds_budget:
+            break
     n_blocks = cfg["num_layers"] + len(range(0, cfg["num_layers"], 2))
     t_blk = sum(times) / len(times)
     tokens_per_s = Ls / (t_blk * n_blocks)
+    L_full = grid[0] * gh * gw
     return dict(value=tokens_per_s, unit="tokens/s", cores=cores, kind="port",
-                sample=f"oracle/restate.dit_block fp32, 1 block of {n_blocks} at dim {D}, batch 1, {Ls} tokens "
-                       f"({sgrid}), {len(times)} run(s), {t_blk:.2f} s/block; tokens/s = {Ls}/(s_per_block*{n_blocks}) "
-                       f"[extrapolated to a full step; attention cost at the real L is ~{(CONFIGS[cfg_name][1][0]*CONFIGS[cfg_name][1][1]*CONFIGS[cfg_name][1][2]//4)//Ls}x larger per token]"), t_blk
+                sample=f"oracle/restate.dit_block fp32 on {cores} threads: 1 block of {n_blocks} at dim {D}, 1 sample, "
+                       f"{Ls} tokens = {sgrid} of the {grid[0]}x{gh}x{gw} grid (frames chosen by a 1-frame calibration "
+                       f"for ~{seconds_budget:.0f} s/block), {len(times)} run(s), {t_blk:.2f} s/block, "
+                       f"{_block_flops(cfg, Ls) / t_blk / 1e12:.2f} TFLOP/s; tokens/s = {Ls}/(s_per_block*{n_blocks})"
+                       + ("" if Ls == L_full else f" [attention cost per token at the full L={L_full} is {L_full / Ls:.1f}x the sample's]")), t_blk
 
 
 def run_reference_arm(args):

@@ -326,6 +326,9 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
     def _peer_exchange(self):
         """Symmetric-memory exchange for the fused Ulysses path; None -> NCCL all_to_all path (VC_SP_MODE=nccl, or
         symmetric memory unavailable on this system — reported once, never silently)."""
+        owner = getattr(self, "_px_owner", None)
+        if owner is not None:  # expert_switch.py: two experts of one process share one exchange
+            return owner._peer_exchange()
         if self._px is None and not self._px_failed:
             if os.environ.get("VC_SP_MODE", "fused") == "nccl":
                 self._px_failed = True
@@ -473,7 +476,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         attn = self._buf("attn", (rows, D))
         if self.sp_world_size > 1 and self._peer_exchange() is not None:
             # Ulysses with both all-to-alls fused into the producer kernels' stores over NVLink (sp.py)
-            attn_sa = sp.ulysses_attention_fused(self._px, qkv, B, Lp, H, self.d, sa.norm_q.weight, sa.norm_k.weight,
+            attn_sa = sp.ulysses_attention_fused(self._peer_exchange(), qkv, B, Lp, H, self.d, sa.norm_q.weight, sa.norm_k.weight,
                                                  st.rope, st.grid, self.eps, max(self.attn_variant, 2))
             ops.gemm(attn_sa, sa.o.weight, sa.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_GATE | ops.EPI_RES, gate=m[:, 2],
                      rows_per_batch=Lp, residual=x2d, out=x2d)
