@@ -103,8 +103,42 @@ int vc_flash_attn_fwd_scatter(const void* q, const void* k, const void* v, int B
  * (wan_transformer3d.py:758-759, wan_transformer3d_versecrafter.py:199-201, :262-263, :340-343). */
 int vc_patchify(const void* in, void* out, int C, int F, int H, int W, long long ld_out, void* stream);
 
+/* K1/K2 — the patch-embedding Conv3d(kernel = stride = (1,2,2)) of ONE sample x[C, F, H, W] as a TMA-fed implicit
+ * GEMM: out[n - tok_lo, :] = sum_{c,ph,pw} x[c, f, 2h+ph, 2w+pw] * weight[:, (c*2 + ph)*2 + pw] + bias for the tokens
+ * n = (f*H/2 + h)*W/2 + w in [tok_lo, tok_hi) (a rank's token range under sequence parallelism).  weight is the
+ * Conv3d weight [D, C, 1, 2, 2] viewed [D, 4C] (row stride ldw), out rows are ldo elements apart.  The input is read
+ * by 4-D TMA boxes of whole patch rows and re-laid out in shared memory as the swizzled K-major MMA operand; no
+ * im2col matrix is written to memory.  Replaces patch_embedding (wan_transformer3d.py:758-759, used
+ * wan_transformer3d_versecrafter.py:340-343) and geoada_patch_embedding (wan_transformer3d_versecrafter.py:199-201,
+ * :262-267) including flatten(2).transpose(1,2).  Shape support (TMA stride/box limits): C % 16 == 0, C <= 128,
+ * H even, W % 8 == 0, W <= 256, D % 8 == 0 — vc_patch_embed_supported returns 1/0; other shapes go through
+ * vc_patchify + vc_gemm_bf16. */
+int vc_patch_embed_supported(int C, int F, int H, int W, int D);
+int vc_patch_embed(const void* x, int C, int F, int H, int W, const void* weight, long long ldw, const void* bias,
+                   int D, void* out, long long ldo, long long tok_lo, long long tok_hi, void* stream);
+
 /* a16 back end — y [L, 4*Co] (row stride ldy) -> out [Co, F, 2*gh, 2*gw]  (unpatchify, wan_transformer3d.py:1127-1150) */
 int vc_unpatchify(const void* y, long long ldy, void* out, int Co, int gf, int gh, int gw, void* stream);
+
+/* N3 — GeoAdapter input assembly (pipeline_wan_versecrafter.py:397-489) in one pass:
+ *   out[s*c_lat + c, f, h, w]            = latents[s][c, f, h, w]                 (torch.cat of the control-video latents)
+ *   out[n_src*c_lat + i*8 + j, f, h, w]  = mask[src_frame[f - n_ref], 8h + i, 8w + j]   for f >= n_ref, 0 before
+ * i.e. geoada_encode_masks' view/permute/reshape to [64, T, Hl, Wl] followed by F.interpolate(mode='nearest-exact') to
+ * Fl - n_ref frames (src_frame = that resampling's source index per output frame, computed by the caller with the
+ * same torch routine) and the zero frames prepended for n_ref reference images, then geoada_latent's channel concat.
+ * latents: n_src device pointers (host array) to bf16 [c_lat, Fl, Hl, Wl]; mask: bf16 [T, 8*Hl, 8*Wl] (channel 0 of
+ * the mask video); out: bf16 [n_src*c_lat + 64, Fl, Hl, Wl]. */
+int vc_control_latents(const void* const* latents, int n_src, int c_lat, const void* mask, int T, int Fl, int Hl,
+                       int Wl, int n_ref, const int* src_frame, void* out, void* stream);
+
+/* N1 — classifier-free-guidance combine + flow-matching Euler update, one pass over the latents
+ * (pipeline_wan_versecrafter.py:903-909; FlowMatchEulerDiscreteScheduler.step of diffusers, not in the reference tree):
+ *   guided = bf16(u + bf16(guidance * bf16(c - u)))      u / c = pred_uncond / pred_text (the two halves of the batch)
+ *   latents_out = bf16(float(latents) + bf16(dt * guided)),   dt = sigma_next - sigma (the caller passes it already
+ *   rounded to bf16: torch's type promotion does that to the 0-dim fp32 dt in `dt * model_output`)
+ * pred_text == NULL: no CFG, guided = pred_uncond.  guided_out may be NULL.  n % 8 == 0 elements, bf16. */
+int vc_cfg_euler_step(const void* pred_uncond, const void* pred_text, const void* latents, void* latents_out,
+                      void* guided_out, long long n, float guidance, float dt, void* stream);
 
 #ifdef __cplusplus
 }

@@ -275,6 +275,40 @@ def test_patchify_unpatchify(ops):
     assert torch.equal(ops.unpatchify(y, (3, 4, 5)), restate.unpatchify(y, (3, 4, 5)))
 
 
+@pytest.mark.parametrize("C,Fr,H,W,D", [(128, 3, 16, 24, 512), (16, 2, 12, 104, 256), (128, 2, 6, 160, 128),
+                                        (16, 5, 30, 56, 1536), (128, 1, 2, 256, 256)])
+def test_patch_embed_implicit_gemm(ops, C, Fr, H, W, D):
+    """Conv3d(kernel = stride = (1,2,2)) as the TMA-fed implicit GEMM vs torch's conv3d in fp32 on the same bf16
+    values (wan_transformer3d_versecrafter.py:262-263, :340-343), vs the explicit patchify + GEMM route, and on
+    token ranges that do not start on a patch-row boundary (a sequence-parallel rank's chunk)."""
+    assert ops.patch_embed_supported(C, Fr, H, W, D)
+    u = _rand((C, Fr, H, W), 40)
+    wt = _rand((D, C, 1, 2, 2), 41, 1.0 / math.sqrt(4 * C))
+    b = _rand((D,), 42, 0.1)
+    L = Fr * (H // 2) * (W // 2)
+    want = torch.nn.functional.conv3d(u.float()[None], wt.float(), b.float(), stride=(1, 2, 2))[0].flatten(1).t()
+    out = torch.full((L, D), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ops.patch_embed(u, wt.view(D, -1), b, out)
+    assert torch.isfinite(out.float()).all()
+    assert relerr(out, want) < 4e-3
+    explicit = ops.gemm(ops.patchify(u), wt.view(D, -1), b)
+    assert relerr(out, explicit) < 1e-3
+    for lo, hi in ((0, L), (37 % L, max(L - 19, 37 % L + 1)), (L // 3, L // 3 + 1), (L - 5, L)):
+        part = torch.full((hi - lo + 3, D), 7.0, device="cuda", dtype=torch.bfloat16)
+        ops.patch_embed(u, wt.view(D, -1), b, part, lo, hi)
+        assert torch.equal(part[:hi - lo], out[lo:hi]), (lo, hi)
+        assert (part[hi - lo:] == 7.0).all()          # nothing stored outside the requested range
+
+
+def test_patch_embed_unsupported_shapes_are_refused(ops):
+    from versecrafter_b200 import _lib
+    assert not ops.patch_embed_supported(16, 5, 30, 52, 512)    # W*2 bytes is not a 16-byte multiple (c1's latent)
+    assert not ops.patch_embed_supported(12, 2, 8, 16, 128)     # C not a multiple of 16
+    u, wt, b = _rand((16, 5, 30, 52), 43), _rand((512, 64), 44), _rand((512,), 45)
+    with pytest.raises(_lib.VCError):
+        ops.patch_embed(u, wt, b, torch.empty(5 * 15 * 26, 512, device="cuda", dtype=torch.bfloat16))
+
+
 def test_errors_are_reported(ops):
     from versecrafter_b200 import _lib
     a, w = _rand((16, 60), 30), _rand((64, 60), 31)

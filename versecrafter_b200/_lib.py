@@ -26,6 +26,10 @@ SIGNATURES = {
                                          _vpp, _i, _i, _c_ll, _vp]),
     "vc_flash_attn_fwd_scatter": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _llp, _llp, _llp, _vpp, _i, _i, _llp, _f, _i,
                                        _vp]),
+    "vc_patch_embed_supported": (_i, [_i, _i, _i, _i, _i]),
+    "vc_patch_embed": (_i, [_vp, _i, _i, _i, _i, _vp, _c_ll, _vp, _i, _vp, _c_ll, _c_ll, _c_ll, _vp]),
+    "vc_control_latents": (_i, [_vpp, _i, _i, _vp, _i, _i, _i, _i, _i, ctypes.POINTER(ctypes.c_int), _vp, _vp]),
+    "vc_cfg_euler_step": (_i, [_vp, _vp, _vp, _vp, _vp, _c_ll, _f, _f, _vp]),
     "vc_patchify": (_i, [_vp, _vp, _i, _i, _i, _i, _c_ll, _vp]),
     "vc_unpatchify": (_i, [_vp, _c_ll, _vp, _i, _i, _i, _i, _vp]),
 }

@@ -200,6 +200,11 @@ void set_error(const char* fmt, ...);
 // for dims 1.. (dim 0 is contiguous).  Returns 0 on success.
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box);
+// general form: element type and shared-memory swizzle chosen by the caller (same dims/strides conventions)
+enum TmapDtype { TMAP_BF16 = 0, TMAP_U32 = 1 };
+enum TmapSwizzle { TMAP_SWIZZLE_NONE = 0, TMAP_SWIZZLE_128B = 1 };
+int make_tmap(CUtensorMap* out, const void* base, TmapDtype dtype, TmapSwizzle swizzle, int rank, const uint64_t* dims,
+              const uint64_t* strides_bytes, const uint32_t* box);
 }  // namespace vc_host
 
 #define VC_CHECK_ARG(cond, ...)        \

@@ -249,6 +249,29 @@ def flash_attn_scatter(q, k, v, peer_ptrs, rows_per_peer, o_strides, softmax_sca
     launch_count += 1
 
 
+def patch_embed_supported(C, Fr, H, W, D):
+    return bool(_lib.load().vc_patch_embed_supported(C, Fr, H, W, D))
+
+
+def patch_embed(u, weight2d, bias, out, tok_lo=0, tok_hi=None):
+    """Conv3d(kernel = stride = (1,2,2)) of one sample u [C, F, H, W] as a TMA-fed implicit GEMM:
+    out[n - tok_lo] = conv(u)[:, n] + bias for tokens n in [tok_lo, tok_hi); weight2d = conv.weight.view(D, 4C)."""
+    global launch_count
+    _chk(u, "u"); _chk(weight2d, "weight"); _chk(bias, "bias"); _chk(out, "out")
+    assert u.dim() == 4 and u.is_contiguous() and weight2d.dim() == 2 and out.dim() == 2
+    C, Fr, H, W = u.shape
+    D = weight2d.shape[0]
+    L = Fr * (H // 2) * (W // 2)
+    tok_hi = L if tok_hi is None else tok_hi
+    assert weight2d.shape[1] == 4 * C and out.shape[1] == D and out.shape[0] >= tok_hi - tok_lo
+    lib = _lib.load()
+    with _timed("patch_embed", 2.0 * (tok_hi - tok_lo) * D * 4 * C):
+        _lib.check(lib.vc_patch_embed(_ptr(u), C, Fr, H, W, _ptr(weight2d), weight2d.stride(0), _ptr(bias), D, _ptr(out),
+                                      out.stride(0), tok_lo, tok_hi, _stream()), "vc_patch_embed")
+    launch_count += 1
+    return out
+
+
 def patchify(u, out=None):
     """u [C, F, H, W] bf16 -> [L, 4C]."""
     global launch_count

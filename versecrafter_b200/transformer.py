@@ -210,6 +210,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         self.sp_world_size, self.sp_world_rank, self.sp_group = 1, 0, None
         self._px, self._px_failed = None, False
         self.attn_variant = int(os.environ.get("VC_ATTN_VARIANT", "4"))
+        self.implicit_patch_embed = os.environ.get("VC_PATCH_EMBED", "implicit") != "explicit"
         self._ws = {}
         self._rope_cache = {}
         self.record = None  # optional dict: tests set it to capture per-block tensors
@@ -447,19 +448,24 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         return ops.gemm(h, t2.weight, t2.bias, out=self._buf("ctx", (B * self.text_len, self.dim)))
 
     def _patch_embed(self, samples, conv, out, seq_len_p, Lp, name):
-        """Conv3d(kernel=stride=(1,2,2)) as patchify + tcgen05 GEMM; only this rank's token rows are produced; rows
-        past the true length are zero (the reference pads after the conv)."""
+        """Conv3d(kernel=stride=(1,2,2)) -> this rank's token rows of `out`; rows past the true length are zero (the
+        reference pads after the conv).  TMA-fed implicit GEMM (vc_patch_embed) whenever the sample meets the TMA
+        stride rules (every latent of a width that is a multiple of 64 pixels); otherwise the patch matrix is written
+        by vc_patchify and multiplied by the tcgen05 GEMM."""
         r0 = self.sp_world_rank * Lp
         w2d = conv.weight.view(self.dim, -1)
         for b, u in enumerate(samples):
             u = u.to(device=self.device, dtype=torch.bfloat16).contiguous()
             C, Fr, H, W = u.shape
             L = Fr * (H // 2) * (W // 2)
-            A = ops.patchify(u, out=self._buf(name, (L, 4 * C)))
             lo, hi = min(r0, L), min(r0 + Lp, L)
             dst = out[b * Lp:(b + 1) * Lp]
             if hi > lo:
-                ops.gemm(A[lo:hi], w2d, conv.bias, out=dst[:hi - lo])
+                if self.implicit_patch_embed and ops.patch_embed_supported(C, Fr, H, W, self.dim):
+                    ops.patch_embed(u, w2d, conv.bias, dst, lo, hi)
+                else:
+                    A = ops.patchify(u, out=self._buf(name, (L, 4 * C)))
+                    ops.gemm(A[lo:hi], w2d, conv.bias, out=dst[:hi - lo])
             if hi - lo < Lp:
                 dst[hi - lo:].zero_()
 
