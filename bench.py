@@ -301,11 +301,20 @@ def run_gpu_arm(args):
     # dominant kernel: self-attention (52 % of the step's FLOPs at c3); algorithmic flops per launch = 4*B*(H/P)*L^2*128
     flops_launch = 4.0 * B * (cfg["num_heads"] / world) * L * L * 128
     achieved = flops_launch / (dom.get("ms_per_launch", float("inf")) * 1e9) if dom else None
-    roofline = {"kernel": "flash_attn_kernel (self-attention)", "bound": "tensor", "achieved": achieved,
+    traffic = None
+    try:  # per-launch DRAM bytes of the dominant kernel from the committed ncu --set full capture of this config
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            ent = json.load(f).get(f"{args.config}:{world}")
+        if ent:
+            traffic = ent["dram_bytes_read"] + ent["dram_bytes_write"]
+    except Exception:  # noqa: BLE001
+        pass
+    roofline = {"kernel": "flash_attn_sa_kernel (self-attention)", "bound": "tensor", "achieved": achieved,
                 "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                 "frac": achieved / peaks["bf16_tflops_sustained"] if achieved else None,
                 "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['source']}); kernel timed inside a long step",
-                "traffic": None, "flops_per_launch": flops_launch, "ms_per_launch": dom.get("ms_per_launch")}
+                "traffic": traffic, "traffic_unit": "bytes/launch (ncu dram__bytes_read.sum + dram__bytes_write.sum)",
+                "flops_per_launch": flops_launch, "ms_per_launch": dom.get("ms_per_launch")}
     line = {"metric": "video_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "s_per_denoise_step": ms_step / 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",

@@ -110,7 +110,8 @@ def test_denoise_loop_matches_stepwise_oracle():
     sig = loop.flow_shift_sigmas(3, 5.0)
     seen = []
     out = loop.denoise(model, x0, geo, inp["context"], sig, guidance_scale=5.0, callback=lambda i, t, x: seen.append(float(t[0])))
-    assert seen == [float(s) * 1000 for s in sig[:-1]] and model.num_inference_steps == 3 and model.current_steps == 2
+    assert seen == pytest.approx([float(s) * 1000 for s in sig[:-1]], rel=1e-6)
+    assert model.num_inference_steps == 3 and model.current_steps == 2
     x = x0
     for i in range(3):
         t = torch.full((2,), float(sig[i]) * 1000, device="cuda")

@@ -136,6 +136,25 @@ def bench_attn_sustained(variant, seconds=4.0, B=2, H=40, L=32760):
               frac_bf16_sustained=flops / (sum(last) / len(last)) / 1e9 / PEAKS["bf16_tflops_sustained"]))
 
 
+def bench_patch_embed(C=128, grid=(21, 60, 104), D=5120):
+    """Control-map patch embedding (K2) at the c3 shape: implicit GEMM vs patchify + GEMM vs torch conv3d (cuDNN)."""
+    Fr, H, W = grid
+    u = torch.randn(C, Fr, H, W, device="cuda", dtype=torch.bfloat16)
+    wt = torch.randn(D, C, 1, 2, 2, device="cuda", dtype=torch.bfloat16) / math.sqrt(4 * C)
+    b = torch.randn(D, device="cuda", dtype=torch.bfloat16)
+    L = Fr * (H // 2) * (W // 2)
+    out = torch.empty(L, D, device="cuda", dtype=torch.bfloat16)
+    A = torch.empty(L, 4 * C, device="cuda", dtype=torch.bfloat16)
+    avg, mn = timeit(lambda: ops.patch_embed(u, wt.view(D, -1), b, out))
+    ex_avg, _ = timeit(lambda: ops.gemm(ops.patchify(u, out=A), wt.view(D, -1), b, out=out))
+    cd_avg, _ = timeit(lambda: torch.nn.functional.conv3d(u[None], wt, b, stride=(1, 2, 2)).flatten(2).transpose(1, 2).contiguous())
+    flops = 2.0 * L * D * 4 * C
+    bytes_ = (u.numel() + out.numel() + wt.numel()) * 2
+    emit(dict(kernel="patch_embed_implicit", shape=[C, Fr, H, W, D], ms=avg, ms_min=mn, tflops=flops / avg / 1e9,
+              gbs=bytes_ / avg / 1e6, frac_hbm=bytes_ / avg / 1e6 / PEAKS["hbm_gbs"],
+              frac_bf16_sustained=flops / avg / 1e9 / PEAKS["bf16_tflops_sustained"], explicit_ms=ex_avg, cudnn_conv3d_ms=cd_avg))
+
+
 if __name__ == "__main__":
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
     which = sys.argv[1:] or ["rows", "gemm", "attn"]
@@ -150,6 +169,9 @@ if __name__ == "__main__":
     if "attn_sustained" in which:
         for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "1,2").split(",")]:
             bench_attn_sustained(variant)
+    if "patch_embed" in which:
+        bench_patch_embed()
+        bench_patch_embed(C=16)
     if "attn_c3" in which:  # the per-launch shape of the c3 step (B=2, 40 heads, 32,760 tokens)
         for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "4").split(",")]:
             bench_attn(2, 40, 32760, 32760, variant)

@@ -9,7 +9,8 @@
 //     dim3 = c  (C, stride F*H*W)
 // One CTA owns an M-tile of R = floor(128 / W') whole patch rows (R*W' <= 128 tokens) and ALL of K = 4C <= 512:
 //   warp 0    : TMA producer — per 16-channel k-block one box {W', 2, R, 16} into a raw staging ring, then the weight
-//               tiles W[n*256 .., kb*64 ..] (128B swizzle) for every N tile into a 2-stage ring (weights stay in L2)
+//               tiles W[n*256 .., kb*64 ..] (128B swizzle) for this CTA's N tiles into a 3-stage ring whose third
+//               stage is the raw staging area, free once the transform is done (weights stay in L2)
 //   warps 2-5 : transform — thread = token row: gathers its 8 x 16 bytes {c, c+1} x {ph} x {pw} from the raw box and
 //               writes them as the canonical K-major SWIZZLE_128B operand tile (what a 2-D TMA of an im2col matrix
 //               would have produced); the A operand (<= 128 KB) then stays resident in smem for all N tiles
@@ -25,7 +26,7 @@ constexpr int BM = 128, BN = 256, BK = 64;
 constexpr int A_BYTES = BM * BK * 2;   // 16 KB canonical A k-block
 constexpr int W_BYTES = BN * BK * 2;   // 32 KB weight tile
 constexpr int RAW_BYTES = 16 * 128 * 8;  // 16 channels x <=128 tokens x (2 ph x 2 pw x bf16) = 16 KB
-constexpr int W_STAGES = 2, RAW_STAGES = 2, MAX_KB = 8;
+constexpr int W_STAGES = 3, RAW_STAGES = 2, MAX_KB = 8;   // W stage 2 aliases the two raw staging buffers
 constexpr int BAR_BYTES = 256;
 constexpr int NUM_THREADS = 192;
 
@@ -37,6 +38,7 @@ struct PEParams {
   int row_lo;     // first patch row (f*H'+h') of tile 0
   int R, Wp;      // patch rows per tile, tokens per patch row
   int N, k_blocks, n_tiles;
+  int n_per_cta;  // N tiles handled by one CTA (blockIdx.y selects the range)
 };
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -44,14 +46,14 @@ patch_embed_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;                                   // k_blocks x 16 KB
-  uint8_t* sW = sA + p.k_blocks * A_BYTES;              // 2 x 32 KB
-  uint8_t* sRaw = sW + W_STAGES * W_BYTES;              // 2 x 16 KB
+  uint8_t* sW = sA + p.k_blocks * A_BYTES;              // 2 x 32 KB (+ stage 2 = sRaw)
+  uint8_t* sRaw = sW + (W_STAGES - 1) * W_BYTES;        // 2 x 16 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(sRaw + RAW_STAGES * RAW_BYTES);
   uint64_t* raw_full = bars;                 // [2]
   uint64_t* raw_empty = raw_full + RAW_STAGES;   // [2]
   uint64_t* a_ready = raw_empty + RAW_STAGES;    // [8]
-  uint64_t* w_full = a_ready + MAX_KB;           // [2]
-  uint64_t* w_empty = w_full + W_STAGES;         // [2]
+  uint64_t* w_full = a_ready + MAX_KB;           // [3]
+  uint64_t* w_empty = w_full + W_STAGES;         // [3]
   uint64_t* acc_full = w_empty + W_STAGES;       // [2]
   uint64_t* acc_empty = acc_full + 2;            // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
@@ -88,6 +90,8 @@ patch_embed_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
   const int tile_row0 = p.row_lo + blockIdx.x * p.R;   // first patch row of this CTA
   const int tile_tokens = p.R * p.Wp;                  // valid A rows (<= 128)
   const uint32_t raw_tx = 16u * (uint32_t)tile_tokens * 8u;
+  const int n_begin = blockIdx.y * p.n_per_cta;
+  const int n_end = min(p.n_tiles, n_begin + p.n_per_cta);
 
   if (warp == 0) {
     // ------------------------------------------------ TMA producer
@@ -100,8 +104,13 @@ patch_embed_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
       }
       int stage = 0;
       uint32_t phase = 0;
-      for (int n = 0; n < p.n_tiles; ++n) {
+      bool raw_free = false;
+      for (int n = n_begin; n < n_end; ++n) {
         for (int kb = 0; kb < p.k_blocks; ++kb) {
+          if (stage == W_STAGES - 1 && !raw_free) {   // stage 2 lives in the raw staging area: wait for the transform
+            for (int i = 0; i < p.k_blocks; ++i) vc::mbar_wait(&a_ready[i], 0);
+            raw_free = true;
+          }
           vc::mbar_wait(&w_empty[stage], phase ^ 1);
           vc::mbar_expect_tx(&w_full[stage], W_BYTES);
           vc::tma_load_2d(sW + stage * W_BYTES, &tmW, &w_full[stage], kb * BK, n * BN);
@@ -120,12 +129,12 @@ patch_embed_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int n = 0; n < p.n_tiles; ++n) {
+      for (int n = n_begin; n < n_end; ++n) {
         vc::mbar_wait(&acc_empty[acc], acc_phase ^ 1);
         vc::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = 0; kb < p.k_blocks; ++kb) {
-          if (n == 0) vc::mbar_wait(&a_ready[kb], 0);   // A k-block transformed (stays resident afterwards)
+          if (n == n_begin) vc::mbar_wait(&a_ready[kb], 0);   // A k-block transformed (stays resident afterwards)
           vc::mbar_wait(&w_full[stage], phase);
           vc::tc_fence_after();
           const uint32_t a0 = vc::smem_u32(sA + kb * A_BYTES);
@@ -182,7 +191,7 @@ patch_embed_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     __nv_bfloat16* crow = p.out + (row_ok ? token - p.tok_lo : 0) * p.ldo;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int n = 0; n < p.n_tiles; ++n) {
+    for (int n = n_begin; n < n_end; ++n) {
       vc::mbar_wait(&acc_full[acc], acc_phase);
       vc::tc_fence_after();
       const uint32_t t_addr = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
@@ -277,7 +286,28 @@ extern "C" int vc_patch_embed(const void* x, int C, int F, int H, int W, const v
   p.tok_lo = tok_lo; p.tok_hi = tok_hi;
   p.row_lo = row_lo; p.R = R; p.Wp = Wp;
   p.N = D; p.k_blocks = 4 * C / BK; p.n_tiles = (D + BN - 1) / BN;
-  const int smem_bytes = p.k_blocks * A_BYTES + W_STAGES * W_BYTES + RAW_STAGES * RAW_BYTES + BAR_BYTES + 1024;
+  // N tiles are split over blockIdx.y when that fills the 148 SMs' waves better (cost model: one transform prologue
+  // ~1.5 N-tile times per CTA, one CTA per SM)
+  int sms = 148;
+  {
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  int best_split = 1;
+  double best_cost = 1e30;
+  for (int split = 1; split <= 4 && split <= p.n_tiles; split *= 2) {
+    const int per = (p.n_tiles + split - 1) / split;
+    const long long ctas = (long long)m_tiles * ((p.n_tiles + per - 1) / per);
+    const double cost = (double)((ctas + sms - 1) / sms) * (1.5 + per);
+    if (cost < best_cost - 1e-9) {
+      best_cost = cost;
+      best_split = split;
+    }
+  }
+  p.n_per_cta = (p.n_tiles + best_split - 1) / best_split;
+  const int n_groups = (p.n_tiles + p.n_per_cta - 1) / p.n_per_cta;
+  const int smem_bytes = p.k_blocks * A_BYTES + (W_STAGES - 1) * W_BYTES + RAW_STAGES * RAW_BYTES + BAR_BYTES + 1024;
   static int attr_set = 0;
   if (attr_set < smem_bytes) {
     cudaError_t e = cudaFuncSetAttribute(patch_embed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
@@ -287,6 +317,6 @@ extern "C" int vc_patch_embed(const void* x, int C, int F, int H, int W, const v
     }
     attr_set = smem_bytes;
   }
-  patch_embed_kernel<<<m_tiles, NUM_THREADS, smem_bytes, (cudaStream_t)stream>>>(tx, tw, p);
+  patch_embed_kernel<<<dim3(m_tiles, n_groups), NUM_THREADS, smem_bytes, (cudaStream_t)stream>>>(tx, tw, p);
   VC_RETURN_LAUNCH_STATUS("vc_patch_embed");
 }
