@@ -203,7 +203,7 @@ def summarize_timing(timing, peaks):
         if tot <= 0:
             continue
         ent = {"launches": len(recs), "ms_total": tot, "ms_per_launch": tot / len(recs)}
-        if name in ("gemm", "attn_self", "attn_cross"):
+        if name in ("gemm", "attn_self", "attn_cross", "patch_embed"):
             ent["tflops"] = work / tot / 1e9
             ent["frac_of_bf16_sustained"] = ent["tflops"] / peaks["bf16_tflops_sustained"]
         else:
