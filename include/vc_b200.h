@@ -140,6 +140,30 @@ int vc_control_latents(const void* const* latents, int n_src, int c_lat, const v
 int vc_cfg_euler_step(const void* pred_uncond, const void* pred_text, const void* latents, void* latents_out,
                       void* guided_out, long long n, float guidance, float dt, void* stream);
 
+/* N4 — per-pixel control-map kernels of /root/reference/inference/rendering_4D_control_maps.py (the parts that are
+ * plain tensor arithmetic there; the pytorch3d point/mesh rasterisers are not built).  Images are uint8 [.., H, W, 3],
+ * depths fp32 [.., H, W], masks uint8 0/1 (torch.bool storage); n_pix = frames*H*W.
+ *
+ * vc_composite_by_depth: composite_by_depth (:438-455) + merge_bg_and_fg_mask (:736-763):
+ *   take_fg = fg_mask & (bg_depth <= 0 | (fg_depth > 0 & fg_depth < bg_depth - 1e-6));  out_rgb / out_depth = fg where
+ *   take_fg else bg;  out_mask_rgb = 255 * (take_fg ? fg_mask : !bg_mask) on 3 channels.  Any output may be NULL.
+ * vc_depth_to_gray: visualize_depth_as_grayscale (:487-539) for a given range: disp = depth > 0 ? 1/depth : 0; if
+ *   normalise: (disp - min_disp) / denom with min_disp = 1/max_depth, denom = 1/min_depth - 1/max_depth + 1e-8 (computed
+ *   by the caller in double, as the reference's python floats); gray = uint8(clamp(.,0,1)*255) on 3 channels.
+ * vc_gaussian_projection: one frame of project_3d_gaussians_to_2d (:573-694, density :765-883) + the blend over the
+ *   background (:697-733) + main()'s masked projection frame: params[k] = {mean_u, mean_v, inv00, inv01, inv10, inv11,
+ *   coeff, r, g, b} (HOST array, Gaussians sorted far -> near, <= 32); density normalised by its image maximum
+ *   (max_scratch: >= 32 uint32 of device memory), thresholded to alpha, composited; outputs (each may be NULL):
+ *   out_rgb uint8, out_alpha fp32, out_blend uint8 (needs bg_rgb), out_masked uint8 = uint8(rgb/255 * alpha * 255). */
+int vc_composite_by_depth(const void* bg_rgb, const void* bg_depth, const void* bg_mask, const void* fg_rgb,
+                          const void* fg_depth, const void* fg_mask, void* out_rgb, void* out_depth, void* out_mask_rgb,
+                          long long n_pix, void* stream);
+int vc_depth_to_gray(const void* depth, void* out_rgb, long long n_pix, float min_disp, float denom, int normalise,
+                     void* stream);
+int vc_gaussian_projection(int n_gauss, const float* params, int W, int H, float threshold, const void* bg_rgb,
+                           void* max_scratch, void* out_rgb, void* out_alpha, void* out_blend, void* out_masked,
+                           void* stream);
+
 #ifdef __cplusplus
 }
 #endif

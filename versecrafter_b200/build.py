@@ -11,7 +11,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libvc_b200.so")
-SOURCES = ["api.cu", "norm_kernels.cu", "gemm_tcgen05.cu", "patch_embed_tcgen05.cu", "loop_glue.cu", "flash_attn_tcgen05.cu"]
+SOURCES = ["api.cu", "norm_kernels.cu", "gemm_tcgen05.cu", "patch_embed_tcgen05.cu", "loop_glue.cu", "control_maps.cu", "flash_attn_tcgen05.cu"]
+# sources whose fp32 divisions / exp must be IEEE / libm-accurate (bit parity with the reference's torch arithmetic)
+PRECISE_SOURCES = {"control_maps.cu"}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "--use_fast_math",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "--expt-relaxed-constexpr",
               "-cudart", "static"]
@@ -42,7 +44,8 @@ def build(force=False, verbose=False):
     procs = []
     for s in SOURCES:
         o = os.path.join(CSRC, s.replace(".cu", ".o"))
-        cmd = [_nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, s), "-o", o]
+        flags = [f for f in NVCC_FLAGS if not (s in PRECISE_SOURCES and f == "--use_fast_math")]
+        cmd = [_nvcc(), *flags, "-c", os.path.join(CSRC, s), "-o", o]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
