@@ -222,20 +222,34 @@ __device__ __forceinline__ float block_sum(float v, float* red) {  // red: ROW_N
 }
 
 template <int VPT>
-__global__ void __launch_bounds__(ROW_NT, VPT <= 4 ? 8 : 7) ln_modulate_block_kernel(
+__global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) ln_modulate_block_kernel(
     const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ p0,
     const __nv_bfloat16* __restrict__ p1, long long mod_stride, long long rows, long long rows_per_batch, int D,
     long long ldx, long long ldo, float eps, int mode) {
   __shared__ float red_a[ROW_NT / 32], red_b[ROW_NT / 32];
   const int nvec = D >> 3;
   const float inv_d = 1.0f / (float)D;
-  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+  // software pipeline: the loads of this CTA's NEXT row are issued before the two block reductions of the current
+  // one, so every resident CTA keeps two rows of HBM reads in flight
+  uint4 raw[VPT], nxt[VPT];
+  long long row = blockIdx.x;
+  if (row < rows) {
     const uint4* xr = reinterpret_cast<const uint4*>(x + row * ldx);
-    uint4 raw[VPT];
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
       const int v = threadIdx.x + ROW_NT * i;
       raw[i] = (v < nvec) ? ld_stream(xr + v) : make_uint4(0, 0, 0, 0);
+    }
+  }
+  for (; row < rows; row += gridDim.x) {
+    const long long nrow = row + gridDim.x;
+    if (nrow < rows) {
+      const uint4* xn = reinterpret_cast<const uint4*>(x + nrow * ldx);
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + ROW_NT * i;
+        nxt[i] = (v < nvec) ? ld_stream(xn + v) : make_uint4(0, 0, 0, 0);
+      }
     }
     float s = 0.f;
 #pragma unroll
@@ -285,13 +299,15 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 4 ? 8 : 7) ln_modulate_block_ke
         st_stream(orow + v, pack8(f));
       }
     }
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) raw[i] = nxt[i];
   }
 }
 
 // Requires (ROW_NT * 8) % head_dim == 0 when rotating: every vector of a thread then sits at the same offset inside
 // its head, so the 4 (cos, sin) pairs are fetched once per row and reused for all VPT vectors and for q and k.
 template <int VPT>
-__global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_block_kernel(
+__global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_block_kernel(
     __nv_bfloat16* __restrict__ qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset, int D,
     const __nv_bfloat16* __restrict__ gq, const __nv_bfloat16* __restrict__ gk, const float2* __restrict__ tab, int Fg,
     int Hg, int Wg, int nf, int nh, int nw, float eps, int do_rope, int n_mats) {
@@ -303,6 +319,17 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_block_k
   const float2* tab_h = tab + (long long)Fg * nf;
   const float2* tab_w = tab_h + (long long)Hg * nh;
   const int j0 = do_rope ? (((threadIdx.x * 8) % (2 * half_d)) >> 1) : 0;
+  // software pipeline over (row, q|k) segments: the next segment's loads are issued before the current one's
+  // reduction, so a CTA always has two segments of HBM reads in flight
+  uint4 raw[VPT], nxt[VPT];
+  if ((long long)blockIdx.x < rows) {
+    const uint4* x0 = reinterpret_cast<const uint4*>(qkv + (long long)blockIdx.x * ld);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + ROW_NT * i;
+      raw[i] = (v < nvec) ? ld_stream_rw(x0 + v) : make_uint4(0, 0, 0, 0);
+    }
+  }
   for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
     const long long pos = pos_offset + (row % rows_per_batch);
     const bool rot = do_rope && pos < (long long)Fg * Hg * Wg;
@@ -323,11 +350,17 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_block_k
     for (int which = 0; which < n_mats; ++which) {
       uint4* xr = reinterpret_cast<uint4*>(qkv + row * ld + (long long)which * D);
       const uint4* gr = reinterpret_cast<const uint4*>(which == 0 ? gq : gk);
-      uint4 raw[VPT];
+      {  // prefetch the next segment: k of this row, else q of this CTA's next row
+        const bool same_row = which + 1 < n_mats;
+        const long long nrow = same_row ? row : row + gridDim.x;
+        if (nrow < rows) {
+          const uint4* xn = reinterpret_cast<const uint4*>(qkv + nrow * ld + (same_row ? (long long)(which + 1) * D : 0));
 #pragma unroll
-      for (int i = 0; i < VPT; ++i) {
-        const int v = threadIdx.x + ROW_NT * i;
-        raw[i] = (v < nvec) ? ld_stream_rw(xr + v) : make_uint4(0, 0, 0, 0);
+          for (int i = 0; i < VPT; ++i) {
+            const int v = threadIdx.x + ROW_NT * i;
+            nxt[i] = (v < nvec) ? ld_stream_rw(xn + v) : make_uint4(0, 0, 0, 0);
+          }
+        }
       }
       float ss = 0.f;
 #pragma unroll
@@ -358,6 +391,8 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_block_k
           st_stream(xr + v, pack8(f));
         }
       }
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) raw[i] = nxt[i];
       if (n_mats == 1) __syncthreads();  // red_a is reused by the next row
     }
   }
