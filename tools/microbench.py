@@ -52,6 +52,10 @@ def bench_rows(B=2, L=32760, D=5120):
     bytes_ = 2 * x.numel() * 2
     emit(dict(kernel="ln_modulate", shape=[B, L, D], ms=avg, ms_min=mn, gbs=bytes_ / avg / 1e6,
               frac_hbm=bytes_ / avg / 1e6 / PEAKS["hbm_gbs"]))
+    gam = torch.randn(D, device="cuda", dtype=torch.bfloat16)
+    avg, mn = timeit(lambda: ops.ln_affine(x, gam, gam, out=out))
+    emit(dict(kernel="ln_affine", shape=[B, L, D], ms=avg, ms_min=mn, gbs=bytes_ / avg / 1e6,
+              frac_hbm=bytes_ / avg / 1e6 / PEAKS["hbm_gbs"]))
     del out
     qkv = torch.randn(B * L, 3 * D, device="cuda", dtype=torch.bfloat16)
     g = torch.ones(D, device="cuda", dtype=torch.bfloat16)

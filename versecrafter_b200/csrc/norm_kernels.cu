@@ -6,6 +6,8 @@
 // One warp owns one row; the row lives in registers between the statistics pass and the write (one HBM read and
 // one HBM write per element), 16-byte vector accesses, warp-shuffle reductions, no shared memory.
 // bf16 rounding points follow the reference's op-by-op autocast arithmetic.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace {
@@ -221,86 +223,132 @@ __device__ __forceinline__ float block_sum(float v, float* red) {  // red: ROW_N
   return t;
 }
 
+// Packed-bf16 helpers.  The reference's op-by-op bf16 arithmetic rounds every product / sum of two bf16 values once;
+// a product of two bf16 values is exact in fp32, so bf16_round(a * b) == HMUL2.BF16 and bf16_round(a + b) == HADD2.BF16
+// (the _rn intrinsics forbid contraction into an fma, which would drop a rounding).  Working on bf16x2 words keeps the
+// row kernels off the quarter-rate F2F conversion pipe: ~8 instructions per element instead of ~32.
+__device__ __forceinline__ __nv_bfloat162 as_bf162(uint32_t u) { return *reinterpret_cast<__nv_bfloat162*>(&u); }
+__device__ __forceinline__ uint32_t as_u32(__nv_bfloat162 v) { return *reinterpret_cast<uint32_t*>(&v); }
+__device__ __forceinline__ float2 up2(uint32_t u) { return vc::unpack_bf16x2(u); }
+__device__ __forceinline__ float vec_sum(const uint4& u) {
+  const float2 a = up2(u.x), b = up2(u.y), c = up2(u.z), d = up2(u.w);
+  return ((a.x + a.y) + (b.x + b.y)) + ((c.x + c.y) + (d.x + d.y));
+}
+__device__ __forceinline__ float vec_sumsq(const uint4& u, float mean, float ss) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float2 f = up2(w[q]);
+    const float d0 = f.x - mean, d1 = f.y - mean;
+    ss = fmaf(d0, d0, ss);
+    ss = fmaf(d1, d1, ss);
+  }
+  return ss;
+}
+
+__device__ __forceinline__ float vec_sumsq0(const uint4& u, float ss) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float2 f = up2(w[q]);
+    ss = fmaf(f.x, f.x, ss);
+    ss = fmaf(f.y, f.y, ss);
+  }
+  return ss;
+}
+// one 16-byte vector of q or k: bf(bf(x * r) * g), then the adjacent-pair rotation in fp32 (one rounding at the pack)
+__device__ __forceinline__ uint4 rms_rope_vec(const uint4& x, __nv_bfloat162 r2, const uint4& g, bool rot, const float2* cs) {
+  const uint32_t xw[4] = {x.x, x.y, x.z, x.w}, gw[4] = {g.x, g.y, g.z, g.w};
+  uint32_t ow[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const __nv_bfloat162 t = __hmul2_rn(__hmul2_rn(as_bf162(xw[q]), r2), as_bf162(gw[q]));
+    if (rot) {
+      const float2 f = __bfloat1622float2(t);
+      ow[q] = vc::pack_bf16x2(f.x * cs[q].x - f.y * cs[q].y, f.x * cs[q].y + f.y * cs[q].x);
+    } else {
+      ow[q] = as_u32(t);
+    }
+  }
+  return make_uint4(ow[0], ow[1], ow[2], ow[3]);
+}
+
 template <int VPT>
-__global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) ln_modulate_block_kernel(
+__global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 2) ln_modulate_block_kernel(
     const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ p0,
     const __nv_bfloat16* __restrict__ p1, long long mod_stride, long long rows, long long rows_per_batch, int D,
     long long ldx, long long ldo, float eps, int mode) {
   __shared__ float red_a[ROW_NT / 32], red_b[ROW_NT / 32];
   const int nvec = D >> 3;
   const float inv_d = 1.0f / (float)D;
-  // software pipeline: the loads of this CTA's NEXT row are issued before the two block reductions of the current
-  // one, so every resident CTA keeps two rows of HBM reads in flight
-  uint4 raw[VPT], nxt[VPT];
-  long long row = blockIdx.x;
-  if (row < rows) {
+  // A thread owns the same columns of every row, so the per-column operands stay in registers while the batch index
+  // does not change: mode 0: sc = bf16(1 + scale), sh = shift;  mode 1: sc = gamma, sh = beta (all packed bf16x2).
+  // (A next-row register prefetch was measured and made no difference once the arithmetic was packed.)
+  uint4 raw[VPT], sc[VPT], sh[VPT];
+  long long cached_batch = -1;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
     const uint4* xr = reinterpret_cast<const uint4*>(x + row * ldx);
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
       const int v = threadIdx.x + ROW_NT * i;
       raw[i] = (v < nvec) ? ld_stream(xr + v) : make_uint4(0, 0, 0, 0);
     }
-  }
-  for (; row < rows; row += gridDim.x) {
-    const long long nrow = row + gridDim.x;
-    if (nrow < rows) {
-      const uint4* xn = reinterpret_cast<const uint4*>(x + nrow * ldx);
+    const long long batch = (mode == 0) ? row / rows_per_batch : 0;
+    if (batch != cached_batch) {
+      cached_batch = batch;
+      const uint4* q0 = reinterpret_cast<const uint4*>(p0 + batch * mod_stride);
+      const uint4* q1 = reinterpret_cast<const uint4*>(p1 + batch * mod_stride);
+      const __nv_bfloat162 one2 = __floats2bfloat162_rn(1.0f, 1.0f);
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
         const int v = threadIdx.x + ROW_NT * i;
-        nxt[i] = (v < nvec) ? ld_stream(xn + v) : make_uint4(0, 0, 0, 0);
+        if (v < nvec) {
+          sh[i] = __ldg(q0 + v);
+          uint4 c = __ldg(q1 + v);
+          if (mode == 0) {
+            c.x = as_u32(__hadd2_rn(one2, as_bf162(c.x)));
+            c.y = as_u32(__hadd2_rn(one2, as_bf162(c.y)));
+            c.z = as_u32(__hadd2_rn(one2, as_bf162(c.z)));
+            c.w = as_u32(__hadd2_rn(one2, as_bf162(c.w)));
+          }
+          sc[i] = c;
+        }
       }
     }
     float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < VPT; ++i) {
-      float f[8];
-      unpack8(raw[i], f);
-      s += ((f[0] + f[1]) + (f[2] + f[3])) + ((f[4] + f[5]) + (f[6] + f[7]));
-    }
+    for (int i = 0; i < VPT; ++i) s += vec_sum(raw[i]);
     const float mean = block_sum(s, red_a) * inv_d;
     float ss = 0.f;
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
-      if (threadIdx.x + ROW_NT * i < nvec) {
-        float f[8];
-        unpack8(raw[i], f);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float d = f[j] - mean;
-          ss = fmaf(d, d, ss);
-        }
-      }
+      if (threadIdx.x + ROW_NT * i < nvec) ss = vec_sumsq(raw[i], mean, ss);
     }
     const float rstd = rsqrtf(block_sum(ss, red_b) * inv_d + eps);
-    const long long moff = (mode == 0) ? (row / rows_per_batch) * mod_stride : 0;
-    const uint4* q0 = reinterpret_cast<const uint4*>(p0 + moff);
-    const uint4* q1 = reinterpret_cast<const uint4*>(p1 + moff);
     uint4* orow = reinterpret_cast<uint4*>(out + row * ldo);
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
       const int v = threadIdx.x + ROW_NT * i;
       if (v < nvec) {
-        float f[8], a[8], c[8];
-        unpack8(raw[i], f);
-        unpack8(__ldg(q0 + v), a);
-        unpack8(__ldg(q1 + v), c);
-        if (mode == 0) {
+        const uint32_t xw[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
+        const uint32_t cw[4] = {sc[i].x, sc[i].y, sc[i].z, sc[i].w};
+        const uint32_t aw[4] = {sh[i].x, sh[i].y, sh[i].z, sh[i].w};
+        uint32_t ow[4];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float ln = bf16_round((f[j] - mean) * rstd);
-            const float sc = bf16_round(1.0f + c[j]);
-            f[j] = bf16_round(ln * sc) + a[j];
+        for (int q = 0; q < 4; ++q) {
+          const float2 f = up2(xw[q]);
+          const float l0 = (f.x - mean) * rstd, l1 = (f.y - mean) * rstd;
+          if (mode == 0) {
+            // bf(bf(bf(ln) * bf(1 + scale)) + shift)
+            ow[q] = as_u32(__hadd2_rn(__hmul2_rn(__floats2bfloat162_rn(l0, l1), as_bf162(cw[q])), as_bf162(aw[q])));
+          } else {
+            const float2 g = up2(cw[q]), bb = up2(aw[q]);
+            ow[q] = vc::pack_bf16x2(fmaf(l0, g.x, bb.x), fmaf(l1, g.y, bb.y));
           }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] = (f[j] - mean) * rstd * c[j] + a[j];
         }
-        st_stream(orow + v, pack8(f));
+        st_stream(orow + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
       }
     }
-#pragma unroll
-    for (int i = 0; i < VPT; ++i) raw[i] = nxt[i];
   }
 }
 
@@ -364,32 +412,13 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_block_k
       }
       float ss = 0.f;
 #pragma unroll
-      for (int i = 0; i < VPT; ++i) {
-        float f[8];
-        unpack8(raw[i], f);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) ss = fmaf(f[j], f[j], ss);
-      }
-      const float r = bf16_round(rsqrtf(block_sum(ss, which ? red_b : red_a) * inv_d + eps));
+      for (int i = 0; i < VPT; ++i) ss = vec_sumsq0(raw[i], ss);
+      const float r = rsqrtf(block_sum(ss, which ? red_b : red_a) * inv_d + eps);
+      const __nv_bfloat162 r2 = __floats2bfloat162_rn(r, r);
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
         const int v = threadIdx.x + ROW_NT * i;
-        if (v < nvec) {
-          float f[8], g[8];
-          unpack8(raw[i], f);
-          unpack8(__ldg(gr + v), g);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] = bf16_round(bf16_round(f[j] * r) * g[j]);
-          if (rot) {
-#pragma unroll
-            for (int p = 0; p < 4; ++p) {
-              const float a = f[2 * p], b = f[2 * p + 1];
-              f[2 * p] = a * cs[p].x - b * cs[p].y;
-              f[2 * p + 1] = a * cs[p].y + b * cs[p].x;
-            }
-          }
-          st_stream(xr + v, pack8(f));
-        }
+        if (v < nvec) st_stream(xr + v, rms_rope_vec(raw[i], r2, __ldg(gr + v), rot, cs));
       }
 #pragma unroll
       for (int i = 0; i < VPT; ++i) raw[i] = nxt[i];
@@ -455,17 +484,13 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_scatter
         const int v = threadIdx.x + ROW_NT * i;
         raw[i] = (v < nvec) ? ld_stream(xr + v) : make_uint4(0, 0, 0, 0);
       }
-      float r = 1.f;
+      __nv_bfloat162 r2 = __floats2bfloat162_rn(1.0f, 1.0f);
       if (which < 2) {
         float ss = 0.f;
 #pragma unroll
-        for (int i = 0; i < VPT; ++i) {
-          float f[8];
-          unpack8(raw[i], f);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) ss = fmaf(f[j], f[j], ss);
-        }
-        r = bf16_round(rsqrtf(block_sum(ss, red[which]) * inv_d + eps));
+        for (int i = 0; i < VPT; ++i) ss = vec_sumsq0(raw[i], ss);
+        const float r = rsqrtf(block_sum(ss, red[which]) * inv_d + eps);
+        r2 = __floats2bfloat162_rn(r, r);
       } else {
         __syncthreads();  // red[0] / red[1] are rewritten by the next row only after everybody read them
       }
@@ -474,22 +499,7 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_scatter
         const int v = threadIdx.x + ROW_NT * i;
         if (v < nvec) {
           uint4 outv = raw[i];
-          if (which < 2) {
-            float f[8], g[8];
-            unpack8(raw[i], f);
-            unpack8(__ldg(gr + v), g);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] = bf16_round(bf16_round(f[j] * r) * g[j]);
-            if (rot) {
-#pragma unroll
-              for (int p = 0; p < 4; ++p) {
-                const float a = f[2 * p], c = f[2 * p + 1];
-                f[2 * p] = a * cs[p].x - c * cs[p].y;
-                f[2 * p + 1] = a * cs[p].y + c * cs[p].x;
-              }
-            }
-            outv = pack8(f);
-          }
+          if (which < 2) outv = rms_rope_vec(raw[i], r2, __ldg(gr + v), rot, cs);
           const int head = v / vec_per_head;
           const int peer = head / heads_per_peer;
           const int hl = head - peer * heads_per_peer;
