@@ -164,6 +164,26 @@ int vc_gaussian_projection(int n_gauss, const float* params, int W, int H, float
                            void* max_scratch, void* out_rgb, void* out_alpha, void* out_blend, void* out_masked,
                            void* stream);
 
+/* N4 — the two rasterisers the reference delegates to pytorch3d (rendering_4D_control_maps.py:150-338), restated from
+ * pytorch3d's published naive algorithms (pytorch3d itself is absent: parity unpinned, oracle/raster_restate.py).
+ * Camera: K = 3x3 pixel intrinsics, T = 4x4 OpenCV world-to-camera (both HOST, row-major fp32), converted as
+ * _build_cam_from_extrinsics (:338-396) + PerspectiveCameras(in_ndc=False) do.  One call renders ONE frame.
+ *
+ * vc_render_points: render_point_cloud_pytorch3d_batch (:243-336): points fp32 [n,3] (world), colors uint8 [n,3];
+ *   per pixel the 8 nearest points (view z >= 0, NDC distance^2 < radius^2) are alpha-composited front to back with
+ *   weights 1 - d^2/r^2, empty pixels get background[3]; out_rgb uint8 [H,W,3], out_depth fp32 [H,W] (nearest z, 0 if
+ *   empty), out_mask uint8 [H,W].  Scratch: proj_scratch >= n*3 fp32, sel_scratch >= 8*H*W uint64.
+ * vc_render_mesh_depth: depth/mask part of render_meshes_pytorch3d_batch (:150-241) (blur_radius 0, 1 face per pixel,
+ *   perspective-correct barycentrics): verts fp32 [n_verts,3] (world), faces int32 [n_faces,3]; out_depth fp32 [H,W],
+ *   out_mask uint8 [H,W], out_pix_to_face int32 [H,W] (may be NULL).  Scratch: vproj_scratch >= n_verts*3 fp32,
+ *   zkey_scratch >= H*W uint64. */
+int vc_render_points(const void* points, const void* colors, long long n_points, const float* K, const float* T, int W,
+                     int H, float radius, const float* background, void* proj_scratch, void* sel_scratch, void* out_rgb,
+                     void* out_depth, void* out_mask, void* stream);
+int vc_render_mesh_depth(const void* verts, int n_verts, const void* faces, int n_faces, const float* K, const float* T,
+                         int W, int H, void* vproj_scratch, void* zkey_scratch, void* out_depth, void* out_mask,
+                         void* out_pix_to_face, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,137 @@
+"""Point-cloud / mesh rasterisers.  pytorch3d is absent, so the oracle is a restatement of its
+published algorithm (parity unpinned, oracle/raster_restate.py): CPU tests check the oracle against closed-form
+geometry, GPU tests check the kernels against the oracle (same fp32 operation order: bit-exact depth / mask / rgb)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import raster_restate as rr
+
+H, W = 36, 64
+K = np.array([[70.0, 0, W / 2 - 1.5], [0, 68.0, H / 2 + 0.75], [0, 0, 1]], dtype=np.float32)
+
+
+def pose(tx=0.0, ty=0.0, tz=0.0, yaw=0.0):
+    T = np.eye(4, dtype=np.float32)
+    c, s = np.cos(yaw), np.sin(yaw)
+    T[:3, :3] = np.array([[c, 0, s], [0, 1, 0], [-s, 0, c]], dtype=np.float32)
+    T[:3, 3] = [tx, ty, tz]
+    return T
+
+
+def cloud(seed, n):
+    g = np.random.default_rng(seed)
+    pts = np.stack([g.uniform(-1.2, 1.2, n), g.uniform(-0.7, 0.7, n), g.uniform(-0.5, 4.0, n)], 1).astype(np.float32)
+    pts[:5, 2] = -1.0                     # behind the camera
+    pts[5:10] = pts[10:15]                # exact duplicates: ties in z broken by index
+    col = g.integers(0, 256, (n, 3)).astype(np.uint8)
+    return pts, col
+
+
+def test_oracle_pixel_grid_and_camera_match_the_pinhole_model():
+    # NDC pixel centres invert to (xi + 0.5, yi + 0.5) pixel coordinates of the OpenCV projection
+    cam = rr.camera(K, pose(), W, H)
+    s = min(W, H) / 2
+    xf = rr.pix_to_ndc(W - 1 - np.arange(W), W, H)
+    yf = rr.pix_to_ndc(H - 1 - np.arange(H), H, W)
+    assert np.allclose(W / 2 - xf * s, np.arange(W) + 0.5, atol=1e-4) and np.allclose(H / 2 - yf * s, np.arange(H) + 0.5, atol=1e-4)
+    p = np.array([[0.3, -0.2, 2.0]], dtype=np.float32)
+    x, y, z = rr.project(p, cam)
+    u, v = K[0, 0] * 0.3 / 2.0 + K[0, 2], K[1, 1] * -0.2 / 2.0 + K[1, 2]
+    assert abs((W / 2 - x[0] * s) - u) < 1e-3 and abs((H / 2 - y[0] * s) - v) < 1e-3 and z[0] == 2.0
+
+
+def test_oracle_single_point_splat_and_compositing_order():
+    # one point at the centre of pixel (10, 20): weight 1 at that pixel, disc of radius r around it, background elsewhere
+    u, v, z = 20.5, 10.5, 2.0
+    p = np.array([[(u - K[0, 2]) * z / K[0, 0], (v - K[1, 2]) * z / K[1, 1], z]], dtype=np.float32)
+    col = np.array([[200, 100, 50]], dtype=np.uint8)
+    r_px = 2.2
+    rgb, depth, mask = rr.render_points(p, col, K, pose(), (H, W), r_px / (min(W, H) / 2))
+    yy, xx = np.mgrid[0:H, 0:W]
+    assert np.array_equal(mask, (xx - 20) ** 2 + (yy - 10) ** 2 < r_px ** 2)
+    assert tuple(rgb[10, 20]) in ((200, 100, 50), (199, 99, 49), (199, 100, 49), (199, 99, 50)) and depth[10, 20] == 2.0
+    assert tuple(rgb[0, 0]) == (127, 127, 127) and depth[0, 0] == 0
+    # a nearer point in front of it wins the depth and dominates the colour
+    p2 = np.concatenate([p, p * np.float32(0.5)])
+    col2 = np.array([[200, 100, 50], [0, 0, 255]], dtype=np.uint8)
+    rgb2, depth2, _ = rr.render_points(p2, col2, K, pose(), (H, W), r_px / (min(W, H) / 2))
+    assert depth2[10, 20] == 1.0 and rgb2[10, 20, 2] >= 254 and rgb2[10, 20, 0] <= 1
+
+
+def test_oracle_sphere_mesh_depth_is_the_analytic_sphere():
+    verts, faces = rr.ellipsoid_mesh([0.1, -0.05, 3.0], 0.04 * np.eye(3), scale_factor=2.0, subdivisions=3)   # radius 0.4
+    depth, mask, p2f = rr.render_mesh_depth(verts, faces, K, pose(), (H, W))
+    yy, xx = np.mgrid[0:H, 0:W]
+    d = np.stack([(xx + 0.5 - K[0, 2]) / K[0, 0], (yy + 0.5 - K[1, 2]) / K[1, 1], np.ones((H, W))], -1)   # ray dirs
+    c = np.array([0.1, -0.05, 3.0])
+    a, b, cc = (d * d).sum(-1), -2 * (d * c).sum(-1), (c * c).sum() - 0.16
+    disc = b * b - 4 * a * cc
+    t = (-b - np.sqrt(np.maximum(disc, 0))) / (2 * a)
+    inside = disc > 0
+    assert (mask & ~inside).sum() == 0 and (inside & ~mask).sum() <= 0.12 * inside.sum()      # faceted sphere is inscribed
+    err = np.abs(depth - t)
+    core = mask & (disc > 0.5 * disc.max())                 # away from the silhouette, where a chord error is amplified
+    assert err[mask].max() < 0.04 and err[core].max() < 0.006 and mask.sum() > 150 and core.sum() > 50
+    assert p2f[mask].min() >= 0 and p2f[~mask].max() == -1
+
+
+def test_host_ico_sphere_matches_oracle():
+    from versecrafter_b200 import raster
+    for lvl in (0, 1, 3):
+        v, f = raster.ico_sphere(lvl)
+        vo, fo = rr.ico_sphere(lvl)
+        assert np.array_equal(v, vo) and np.array_equal(f, fo) and len(f) == 20 * 4 ** lvl
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,radius,T", [(3000, 0.06, pose()), (3000, 0.11, pose(0.2, -0.1, 0.3, 0.2)), (40, 0.3, pose())])
+def test_point_renderer_matches_oracle(n, radius, T):
+    from versecrafter_b200 import raster
+    pts, col = cloud(n, n)
+    rgb, depth, mask = raster.render_point_cloud_batch(torch.from_numpy(pts).cuda(), torch.from_numpy(col).cuda(), [K], [T],
+                                                       (H, W), point_size=radius)
+    want_rgb, want_depth, want_mask = rr.render_points(pts, col, K, T, (H, W), radius)
+    assert np.array_equal(mask[0].cpu().numpy(), want_mask)
+    assert np.array_equal(depth[0].cpu().numpy(), want_depth)
+    assert np.array_equal(rgb[0].cpu().numpy(), want_rgb)
+
+
+@pytest.mark.gpu
+def test_point_renderer_handles_bad_points_and_empty_clouds():
+    from versecrafter_b200 import raster
+    pts, col = cloud(3, 500)
+    bad = pts.copy()
+    bad[100] = [np.nan, 0, 1]
+    bad[101] = [np.inf, 0, 1]
+    keep = np.ones(500, bool)
+    keep[[100, 101]] = False
+    rgb, depth, mask = raster.render_point_cloud_batch(torch.from_numpy(bad).cuda(), torch.from_numpy(col).cuda(), [K], [pose()],
+                                                       (H, W), point_size=0.08)
+    want = rr.render_points(pts[keep], col[keep], K, pose(), (H, W), 0.08)
+    assert np.array_equal(rgb[0].cpu().numpy(), want[0]) and np.array_equal(depth[0].cpu().numpy(), want[1])
+    rgb0, depth0, mask0 = raster.render_point_cloud_batch(torch.zeros(0, 3).cuda(), torch.zeros(0, 3, dtype=torch.uint8).cuda(),
+                                                          [K, K], [pose(), pose()], (H, W))
+    assert (rgb0 == 127).all() and (depth0 == 0).all() and not mask0.any()
+
+
+@pytest.mark.gpu
+def test_mesh_depth_renderer_matches_oracle():
+    from versecrafter_b200 import raster
+    covs = [np.diag([0.05, 0.02, 0.03]).astype(np.float32), np.array([[0.03, 0.01, 0], [0.01, 0.04, 0.005], [0, 0.005, 0.02]], np.float32)]
+    means = [[-0.3, 0.1, 2.5], [0.35, -0.1, 3.2]]
+    frames, oracle = [], []
+    Ts = [pose(), pose(0.1, 0.0, -0.2, -0.15), pose()]
+    for b, T in enumerate(Ts):
+        if b == 2:
+            frames.append(None)
+            continue
+        parts = [raster.make_ellipsoid_mesh(m, c, scale_factor=2.5, subdivisions=2) for m, c in zip(means, covs)]
+        v, f = raster.combine_meshes_for_scene(parts)
+        frames.append((v, f))
+        oracle.append(rr.render_mesh_depth(v.cpu().numpy(), f.cpu().numpy(), K, T, (H, W)))
+    depth, mask = raster.render_meshes_depth_batch(frames, [K] * 3, Ts, (H, W))
+    for b in range(2):
+        assert np.array_equal(mask[b].cpu().numpy(), oracle[b][1]) and oracle[b][1].sum() > 100
+        assert np.array_equal(depth[b].cpu().numpy(), oracle[b][0])
+    assert not mask[2].any() and (depth[2] == 0).all()

@@ -12,6 +12,7 @@ _i = ctypes.c_int
 _f = ctypes.c_float
 _llp = ctypes.POINTER(ctypes.c_longlong)
 _vpp = ctypes.POINTER(ctypes.c_void_p)
+_fp = ctypes.POINTER(ctypes.c_float)
 
 SIGNATURES = {
     "vc_version": (_i, []),
@@ -33,6 +34,8 @@ SIGNATURES = {
     "vc_composite_by_depth": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _c_ll, _vp]),
     "vc_depth_to_gray": (_i, [_vp, _vp, _c_ll, _f, _f, _i, _vp]),
     "vc_gaussian_projection": (_i, [_i, ctypes.POINTER(ctypes.c_float), _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "vc_render_points": (_i, [_vp, _vp, _c_ll, _fp, _fp, _i, _i, _f, _fp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "vc_render_mesh_depth": (_i, [_vp, _i, _vp, _i, _fp, _fp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "vc_patchify": (_i, [_vp, _vp, _i, _i, _i, _i, _c_ll, _vp]),
     "vc_unpatchify": (_i, [_vp, _c_ll, _vp, _i, _i, _i, _i, _vp]),
 }
