@@ -221,8 +221,8 @@ Cam make_cam(const float* K, const float* T, int W, int H) {
 extern "C" int vc_render_points(const void* points, const void* colors, long long n_points, const float* K, const float* T,
                                 int W, int H, float radius, const float* background, void* proj_scratch,
                                 void* sel_scratch, void* out_rgb, void* out_depth, void* out_mask, void* stream) {
-  VC_CHECK_ARG(points && colors && K && T && background && proj_scratch && sel_scratch && out_rgb && out_depth && out_mask,
-               "vc_render_points: null operand");
+  VC_CHECK_ARG(K && T && background && sel_scratch && out_rgb && out_depth && out_mask, "vc_render_points: null operand");
+  VC_CHECK_ARG(n_points <= 0 || (points && colors && proj_scratch), "vc_render_points: null point cloud operand");
   VC_CHECK_ARG(n_points >= 0 && n_points < 0xFFFFFFFFll && W > 0 && H > 0 && radius > 0.0f,
                "vc_render_points: bad sizes n=%lld W=%d H=%d radius=%g", n_points, W, H, (double)radius);
   cudaStream_t s = (cudaStream_t)stream;
