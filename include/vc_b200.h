@@ -140,6 +140,20 @@ int vc_control_latents(const void* const* latents, int n_src, int c_lat, const v
 int vc_cfg_euler_step(const void* pred_uncond, const void* pred_text, const void* latents, void* latents_out,
                       void* guided_out, long long n, float guidance, float dt, void* stream);
 
+/* N1 — CFG combine + one step of the flow-matching UniPC multistep scheduler (predict-x0, B(h)=expm1(h), solver order
+ * <= 2: corrector on the incoming sample, then predictor), one pass over the latents.  Replaces
+ * `self.scheduler.step(noise_pred, t, latents)` for the reference's default sampler "Flow_Unipc"
+ * (/root/reference/inference/versecrafter_inference.py:135,:254; pipeline_wan_versecrafter.py:903-909; the class is
+ * videox_fun.utils.fm_solvers_unipc.FlowUniPCMultistepScheduler, un-vendored).
+ *   latents (bf16, n elements) = the sample the model was evaluated on; last/m0/m1 (fp32) = the previous step's
+ *   corrected sample and the two most recent x0 predictions (NULL where the order does not need them);
+ *   x0_out / last_out (fp32) receive this step's x0 prediction and corrected sample (the caller rotates the history);
+ *   coef = 13 host floats {sigma, corr_order, c_x, c_m0, c_bh, c_rho0, c_rk, c_rhot, pred_order, p_x, p_m0, p_bh, p_rk}
+ *   (formula in csrc/loop_glue.cu; versecrafter_b200/schedulers.py computes them).  n % 4 == 0. */
+int vc_cfg_unipc_step(const void* pred_uncond, const void* pred_text, const void* latents, const void* last,
+                      const void* m0, const void* m1, void* latents_out, void* x0_out, void* last_out, long long n,
+                      float guidance, const float* coef, void* stream);
+
 /* N4 — per-pixel control-map kernels of /root/reference/inference/rendering_4D_control_maps.py (the parts that are
  * plain tensor arithmetic there; the pytorch3d point/mesh rasterisers are not built).  Images are uint8 [.., H, W, 3],
  * depths fp32 [.., H, W], masks uint8 0/1 (torch.bool storage); n_pix = frames*H*W.

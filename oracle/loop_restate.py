@@ -58,3 +58,103 @@ def flow_shift_sigmas(num_steps, shift=5.0, num_train_timesteps=1000):
     t = torch.linspace(float(smax) * num_train_timesteps, float(smin) * num_train_timesteps, num_steps, dtype=torch.float64)
     s = sh(t / num_train_timesteps)
     return torch.cat([s, torch.zeros(1, dtype=torch.float64)]).float()
+
+
+class FlowUniPCOracle:
+    """Flow-matching UniPC multistep scheduler (predict-x0, `bh2`, solver order 2, lower_order_final, final sigma 0) —
+    the reference's default sampler (`sampler_name = "Flow_Unipc"`, /root/reference/inference/versecrafter_inference.py
+    :135,:254; driven at pipeline_wan_versecrafter.py:750-752,:909).  The class itself is
+    `videox_fun.utils.fm_solvers_unipc.FlowUniPCMultistepScheduler` (VideoX-Fun, un-vendored, no recoverable pin; a
+    flow-matching adaptation of diffusers' UniPCMultistepScheduler): **parity unpinned**.  This restates the published
+    UniPC algorithm (Zhao et al. 2023, B(h) = expm1(h) variant) in the structure of that scheduler — model-output
+    history list, per-step R/b system, einsum over the D1 stack — in fp32 torch ops."""
+
+    def __init__(self, num_train_timesteps=1000, solver_order=2, shift=1.0):
+        self.N, self.solver_order, self.shift = num_train_timesteps, solver_order, shift
+        alphas = torch.linspace(1, 1 / num_train_timesteps, num_train_timesteps, dtype=torch.float64).flip(0)
+        sig = 1.0 - alphas
+        sig = shift * sig / (1 + (shift - 1) * sig)
+        self.sigma_min, self.sigma_max = float(sig[-1].float()), float(sig[0].float())
+
+    def set_timesteps(self, num_inference_steps, shift=None):
+        shift = self.shift if shift is None else shift
+        import numpy as np
+        s = np.linspace(self.sigma_max, self.sigma_min, num_inference_steps + 1)[:-1]
+        s = shift * s / (1 + (shift - 1) * s)
+        self.timesteps = torch.from_numpy(s * self.N).to(torch.int64)
+        self.sigmas = torch.from_numpy(np.concatenate([s, [0.0]]).astype(np.float32))
+        self.model_outputs = [None] * self.solver_order
+        self.lower_order_nums, self.last_sample, self.step_index, self.this_order = 0, None, 0, 1
+
+    @staticmethod
+    def _lam(sigma):
+        return torch.log(1 - sigma) - torch.log(sigma)
+
+    def _rb(self, rks, hh, order):
+        h_phi_1 = torch.expm1(hh)
+        h_phi_k = h_phi_1 / hh - 1
+        B_h = torch.expm1(hh)
+        R, b, fact = [], [], 1
+        for i in range(1, order + 1):
+            R.append(torch.pow(rks, i - 1))
+            b.append(h_phi_k * fact / B_h)
+            fact *= i + 1
+            h_phi_k = h_phi_k / hh - 1 / fact
+        return torch.stack(R), torch.stack(b), h_phi_1, B_h
+
+    def _d1s(self, first_back, order, lam_s0, h, m0):
+        rks, d1s = [], []
+        for i in range(1, order):
+            si = self.step_index - first_back - (i - 1)
+            mi = self.model_outputs[-(i + 1)]
+            rk = (self._lam(self.sigmas[si]) - lam_s0) / h
+            rks.append(rk)
+            d1s.append((mi - m0) / rk)
+        rks.append(torch.tensor(1.0))
+        return torch.stack(rks), (torch.stack(d1s, dim=1) if d1s else None)
+
+    def _predict(self, sample, order):
+        m0, x = self.model_outputs[-1], sample
+        sigma_t, sigma_s0 = self.sigmas[self.step_index + 1], self.sigmas[self.step_index]
+        alpha_t = 1 - sigma_t
+        lam_s0 = self._lam(sigma_s0)
+        h = self._lam(sigma_t) - lam_s0
+        rks, D1s = self._d1s(1, order, lam_s0, h, m0)
+        R, b, h_phi_1, B_h = self._rb(rks, -h, order)
+        x_t_ = sigma_t / sigma_s0 * x - alpha_t * h_phi_1 * m0
+        if D1s is None:
+            return x_t_
+        rhos_p = torch.tensor([0.5]) if order == 2 else torch.linalg.solve(R[:-1, :-1], b[:-1])
+        pred_res = torch.einsum("k,bkc...->bc...", rhos_p, D1s)
+        return x_t_ - alpha_t * B_h * pred_res
+
+    def _correct(self, model_t, last_sample, order):
+        m0, x = self.model_outputs[-1], last_sample
+        sigma_t, sigma_s0 = self.sigmas[self.step_index], self.sigmas[self.step_index - 1]
+        alpha_t = 1 - sigma_t
+        lam_s0 = self._lam(sigma_s0)
+        h = self._lam(sigma_t) - lam_s0
+        rks, D1s = self._d1s(2, order, lam_s0, h, m0)
+        R, b, h_phi_1, B_h = self._rb(rks, -h, order)
+        rhos_c = torch.tensor([0.5]) if order == 1 else torch.linalg.solve(R, b)
+        x_t_ = sigma_t / sigma_s0 * x - alpha_t * h_phi_1 * m0
+        corr_res = torch.einsum("k,bkc...->bc...", rhos_c[:-1], D1s) if D1s is not None else 0
+        return x_t_ - alpha_t * B_h * (corr_res + rhos_c[-1] * (model_t - m0))
+
+    def step(self, model_output, sample):
+        """model_output = the (CFG-combined) velocity prediction at sigmas[step_index]; returns the next sample in
+        sample.dtype.  State (x0 history, last sample) is fp32."""
+        out_dtype = sample.dtype
+        sample = sample.float()
+        x0 = sample - self.sigmas[self.step_index] * model_output.float()           # flow prediction -> x0
+        if self.step_index > 0 and self.last_sample is not None:
+            sample = self._correct(x0, self.last_sample, self.this_order)
+        self.model_outputs = self.model_outputs[1:] + [x0]
+        this_order = min(self.solver_order, len(self.timesteps) - self.step_index)   # lower_order_final
+        self.this_order = min(this_order, self.lower_order_nums + 1)
+        self.last_sample = sample
+        prev = self._predict(sample, self.this_order)
+        if self.lower_order_nums < self.solver_order:
+            self.lower_order_nums += 1
+        self.step_index += 1
+        return prev.to(out_dtype)

@@ -118,3 +118,141 @@ def test_denoise_loop_matches_stepwise_oracle():
         pred = model(x=torch.cat([x, x]), t=t, geoada_context=[geo, geo], context=inp["context"], seq_len=inp["seq_len"])
         x = lr.euler_step(lr.cfg_combine(pred[0:1], pred[1:2], 5.0), x, sig[i], sig[i + 1])
     assert torch.equal(out, x)
+
+
+# ---- flow-matching UniPC (the reference's default sampler; upstream class un-vendored: parity unpinned) ----------
+def _kernel_formula(coef, u, c, x, last, m0, m1, guidance):
+    """The arithmetic of cfg_unipc_step_kernel (csrc/loop_glue.cu) written with torch fp32 ops in the same order."""
+    f = lambda v: torch.tensor(v, dtype=torch.float32)
+    v = u if c is None else lr.cfg_combine(u, c, guidance)
+    x, v = x.float(), v.float()
+    x0 = x - f(coef[0]) * v
+    xc = x
+    if int(coef[1]) >= 1:
+        res = f(coef[7]) * (x0 - m0)
+        if int(coef[1]) == 2:
+            res = f(coef[5]) * ((m1 - m0) / f(coef[6])) + res
+        xc = (f(coef[2]) * last - f(coef[3]) * m0) - f(coef[4]) * res
+    out = f(coef[9]) * xc - f(coef[10]) * x0
+    if int(coef[8]) == 2:
+        out = out - f(coef[11]) * (f(0.5) * ((m0 - x0) / f(coef[12])))
+    return out, x0, xc
+
+
+def test_unipc_oracle_properties():
+    """An exact straight-path velocity is integrated exactly at every order; a nonlinear field converges at order 2."""
+    torch.manual_seed(0)
+    x0, n = torch.randn(1, 4, 3, 8, 8), torch.randn(1, 4, 3, 8, 8)
+    for steps, shift in ((10, 16.0), (5, 1.0), (3, 5.0), (2, 3.0), (1, 3.0)):
+        s = lr.FlowUniPCOracle()
+        s.set_timesteps(steps, shift=shift)
+        assert s.timesteps[0] == 999 and float(s.sigmas[-1]) == 0.0 and len(s.sigmas) == steps + 1
+        x = (1 - s.sigmas[0]) * x0 + s.sigmas[0] * n
+        for _ in range(steps):
+            x = s.step(n - x0, x)
+        assert float((x - x0).abs().max()) < 5e-6
+
+    def run(steps):
+        s = lr.FlowUniPCOracle()
+        s.set_timesteps(steps, shift=1.0)
+        x = torch.ones(1, 1, 1, 1, 1)
+        for i in range(steps):
+            x = s.step(torch.sin(3 * x) + s.sigmas[i], x)
+        return float(x)
+    ref = run(2000)
+    e = [abs(run(k) - ref) for k in (10, 20, 40)]
+    assert 3.0 < e[0] / e[1] < 5.0 and 3.0 < e[1] / e[2] < 5.0        # error / 4 when the step halves
+
+
+@pytest.mark.parametrize("steps,shift,order", [(8, 16.0, 2), (3, 5.0, 2), (2, 1.0, 2), (1, 3.0, 2), (6, 3.0, 1)])
+def test_unipc_host_coefficients_match_oracle(steps, shift, order):
+    """schedulers.FlowUniPCMultistepScheduler's per-step scalars, pushed through the kernel's formula on CPU, follow
+    the oracle over a whole loop (timesteps / sigmas identical)."""
+    from versecrafter_b200 import schedulers
+    sch = schedulers.FlowUniPCMultistepScheduler(shift=1, solver_order=order)
+    sch.set_timesteps(steps, shift=shift)
+    orc = lr.FlowUniPCOracle(solver_order=order)
+    orc.set_timesteps(steps, shift=shift)
+    assert torch.equal(sch.timesteps, orc.timesteps) and torch.equal(sch.sigmas, orc.sigmas)
+    assert sch.order == 1 and sch.init_noise_sigma == 1.0
+    g = torch.Generator().manual_seed(steps)
+    x = torch.randn(1, 16, 2, 6, 8, generator=g).bfloat16()
+    last = m0 = m1 = None
+    sch._state = dict(have_last=False)
+    for i in range(steps):
+        u, c = (torch.randn(x.shape, generator=g).bfloat16() for _ in range(2))
+        coef, op = sch._coefficients()
+        out, x0, xc = _kernel_formula(coef, u, c, x, last, m0, m1, 5.0)
+        m1, m0, last = m0, x0, xc
+        sch._state["have_last"] = True
+        sch._this_order = op
+        sch._lower_order_nums = min(sch._lower_order_nums + 1, sch.solver_order)
+        sch._step_index += 1
+        want = orc.step(lr.cfg_combine(u, c, 5.0), x)       # same input sample on both sides: per-step agreement
+        assert torch.allclose(x0, orc.model_outputs[-1], rtol=1e-5, atol=1e-5)
+        assert torch.allclose(xc, orc.last_sample, rtol=1e-4, atol=1e-4)
+        x = out.bfloat16()
+        d = (x.float() - want.float()).abs()                # fp32 values a few ulps apart -> rare 1-ulp bf16 flips
+        assert float(d.max()) <= 2 ** -7 * max(1.0, float(want.float().abs().max())) and float((d > 0).float().mean()) < 0.01
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("steps,shift,cfg", [(8, 16.0, True), (3, 5.0, True), (1, 3.0, False), (5, 1.0, False)])
+def test_unipc_kernel_matches_oracle(steps, shift, cfg):
+    """vc_cfg_unipc_step over a whole loop == the oracle (fp32 state on both sides; host scalars are float64 on one
+    side and fp32 torch on the other: agreement to a few fp32 ulps before the bf16 output rounding)."""
+    from versecrafter_b200 import schedulers
+    sch = schedulers.FlowUniPCMultistepScheduler(shift=1)
+    sch.set_timesteps(steps, device="cuda", shift=shift)
+    orc = lr.FlowUniPCOracle()
+    orc.set_timesteps(steps, shift=shift)
+    assert torch.equal(sch.timesteps.cpu(), orc.timesteps)
+    g = torch.Generator(device="cuda").manual_seed(31)
+    shape = (1, 16, 5, 30, 52)
+    x = torch.randn(shape, generator=g, device="cuda").bfloat16()
+    for i in range(steps):
+        u, c = (torch.randn(shape, generator=g, device="cuda").bfloat16() for _ in range(2))
+        got = sch.step_cfg(u, c if cfg else None, x, 5.0)
+        v = lr.cfg_combine(u, c, 5.0) if cfg else u
+        want = orc.step(v.cpu(), x.cpu())
+        assert torch.allclose(sch._state["m0"].view(shape).cpu(), orc.model_outputs[-1], rtol=1e-5, atol=1e-5)
+        assert torch.allclose(sch._state["last"].view(shape).cpu(), orc.last_sample, rtol=1e-4, atol=1e-4)
+        d = (got.cpu().float() - want.float()).abs()
+        assert float(d.max()) <= 2 ** -7 * max(1.0, float(want.float().abs().max()))      # at most one bf16 ulp
+        assert float((d > 0).float().mean()) < 0.01
+        x = got
+    with pytest.raises(Exception):
+        sch.step_cfg(u, None, x)                        # more steps than set_timesteps announced
+    # the pipeline-compatible entry: step(model_output, t, sample, return_dict=False)
+    sch.set_timesteps(2, device="cuda", shift=shift)
+    y = sch.step(u, sch.timesteps[0], x, return_dict=False)[0]
+    assert y.shape == x.shape and y.dtype == torch.bfloat16 and bool(torch.isfinite(y.float()).all())
+
+
+@pytest.mark.gpu
+def test_denoise_loop_unipc():
+    """denoise(scheduler=UniPC) == the same loop written with the oracle scheduler around the same transformer calls."""
+    from oracle import restate
+    from versecrafter_b200 import loop, schedulers
+    from versecrafter_b200.transformer import VerseCrafterWanTransformer3DModel
+    cfg = dict(dim=256, ffn_dim=512, num_heads=2, num_layers=2, text_dim=64, geoada_in_dim=128)
+    sd = restate.synth_state_dict(cfg, seed=4, device="cuda", dtype=torch.bfloat16)
+    model = VerseCrafterWanTransformer3DModel(**cfg, device="cuda", dtype=torch.bfloat16, init=False)
+    model.load_state_dict(sd, strict=True)
+    inp = restate.synth_inputs(cfg, (2, 8, 16), seed=4, device="cuda")
+    x0 = inp["x"][:1].bfloat16()
+    geo = inp["geoada_context"][0].bfloat16()
+    sch = schedulers.FlowUniPCMultistepScheduler(shift=1)
+    sch.set_timesteps(4, device="cuda", shift=16.0)
+    out = loop.denoise(model, x0, geo, inp["context"], guidance_scale=5.0, scheduler=sch)
+    orc = lr.FlowUniPCOracle()
+    orc.set_timesteps(4, shift=16.0)
+    x = x0
+    for i in range(4):
+        t = orc.timesteps[i].cuda().expand(2)
+        pred = model(x=torch.cat([x, x]), t=t, geoada_context=[geo, geo], context=inp["context"], seq_len=inp["seq_len"])
+        x = orc.step(lr.cfg_combine(pred[0:1], pred[1:2], 5.0).cpu(), x.cpu()).cuda()
+    cos = torch.nn.functional.cosine_similarity(out.float().flatten(), x.float().flatten(), dim=0)
+    assert float(cos) > 0.9999
+    with pytest.raises(Exception):
+        loop.denoise(model, x0, geo, inp["context"])     # neither sigmas nor scheduler

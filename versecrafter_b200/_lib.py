@@ -31,6 +31,7 @@ SIGNATURES = {
     "vc_patch_embed": (_i, [_vp, _i, _i, _i, _i, _vp, _c_ll, _vp, _i, _vp, _c_ll, _c_ll, _c_ll, _vp]),
     "vc_control_latents": (_i, [_vpp, _i, _i, _vp, _i, _i, _i, _i, _i, ctypes.POINTER(ctypes.c_int), _vp, _vp]),
     "vc_cfg_euler_step": (_i, [_vp, _vp, _vp, _vp, _vp, _c_ll, _f, _f, _vp]),
+    "vc_cfg_unipc_step": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _c_ll, _f, _fp, _vp]),
     "vc_composite_by_depth": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _c_ll, _vp]),
     "vc_depth_to_gray": (_i, [_vp, _vp, _c_ll, _f, _f, _i, _vp]),
     "vc_gaussian_projection": (_i, [_i, ctypes.POINTER(ctypes.c_float), _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -101,6 +101,74 @@ __global__ void __launch_bounds__(256) cfg_euler_step_kernel(const __nv_bfloat16
   }
 }
 
+// CFG combine + flow-matching UniPC (predict-x0, bh2, order <= 2) corrector and predictor in one pass over the latents.
+// Per element, fp32 (state m0/m1/last are fp32; every product/sum is a separate rounding, no contraction, so a torch
+// fp32 restatement with the same op order agrees to the last bit given the same scalars):
+//   v   = CFG(u, c)                                   (bf16 rounding points of the pipeline's expression)
+//   x0  = x - sigma * v                               (flow prediction -> data prediction)
+//   xc  = corr ? (c_x*last - c_m0*m0) - c_bh*(c_rho0*((m1-m0)/c_rk) + c_rhot*(x0-m0)) : x
+//   out = (p_x*xc - p_m0*x0) - p_bh*(0.5*((m0-x0)/p_rk))        [last term only at predictor order 2]
+// The x0 history rotates on the host: x0_out becomes m0, the old m0 becomes m1; last_out = xc.
+struct UniPCCoef {
+  float sigma;
+  int corr_order;  // 0 = no corrector (first step)
+  float c_x, c_m0, c_bh, c_rho0, c_rk, c_rhot;
+  int pred_order;
+  float p_x, p_m0, p_bh, p_rk;
+};
+
+__global__ void __launch_bounds__(256) cfg_unipc_step_kernel(const __nv_bfloat16* __restrict__ pred_uncond,
+                                                            const __nv_bfloat16* __restrict__ pred_text,
+                                                            const __nv_bfloat16* __restrict__ latents,
+                                                            const float* __restrict__ last, const float* __restrict__ m0,
+                                                            const float* __restrict__ m1,
+                                                            __nv_bfloat16* __restrict__ latents_out,
+                                                            float* __restrict__ x0_out, float* __restrict__ last_out,
+                                                            long long n_vec, float guidance, int use_cfg, UniPCCoef k) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += (long long)gridDim.x * blockDim.x) {
+    const uint2 uu = __ldg(reinterpret_cast<const uint2*>(pred_uncond) + i);
+    const uint2 xx = __ldg(reinterpret_cast<const uint2*>(latents) + i);
+    uint2 cc = uu;
+    if (use_cfg) cc = __ldg(reinterpret_cast<const uint2*>(pred_text) + i);
+    const float2 u01 = vc::unpack_bf16x2(uu.x), u23 = vc::unpack_bf16x2(uu.y);
+    const float2 c01 = vc::unpack_bf16x2(cc.x), c23 = vc::unpack_bf16x2(cc.y);
+    const float2 x01 = vc::unpack_bf16x2(xx.x), x23 = vc::unpack_bf16x2(xx.y);
+    const float u[4] = {u01.x, u01.y, u23.x, u23.y}, c[4] = {c01.x, c01.y, c23.x, c23.y};
+    const float x[4] = {x01.x, x01.y, x23.x, x23.y};
+    float4 lv = make_float4(0.f, 0.f, 0.f, 0.f), m0v = lv, m1v = lv;
+    if (k.corr_order >= 1) {
+      lv = __ldg(reinterpret_cast<const float4*>(last) + i);
+      m0v = __ldg(reinterpret_cast<const float4*>(m0) + i);
+    } else if (k.pred_order == 2) {
+      m0v = __ldg(reinterpret_cast<const float4*>(m0) + i);
+    }
+    if (k.corr_order == 2) m1v = __ldg(reinterpret_cast<const float4*>(m1) + i);
+    const float la[4] = {lv.x, lv.y, lv.z, lv.w}, m0a[4] = {m0v.x, m0v.y, m0v.z, m0v.w};
+    const float m1a[4] = {m1v.x, m1v.y, m1v.z, m1v.w};
+    float x0a[4], xca[4], oa[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float v = u[q];
+      if (use_cfg) v = vc::bf16_round(u[q] + vc::bf16_round(guidance * vc::bf16_round(c[q] - u[q])));
+      const float x0 = __fsub_rn(x[q], __fmul_rn(k.sigma, v));
+      float xc = x[q];
+      if (k.corr_order >= 1) {
+        const float xt = __fsub_rn(__fmul_rn(k.c_x, la[q]), __fmul_rn(k.c_m0, m0a[q]));
+        float res = __fmul_rn(k.c_rhot, __fsub_rn(x0, m0a[q]));
+        if (k.corr_order == 2) res = __fadd_rn(__fmul_rn(k.c_rho0, __fdiv_rn(__fsub_rn(m1a[q], m0a[q]), k.c_rk)), res);
+        xc = __fsub_rn(xt, __fmul_rn(k.c_bh, res));
+      }
+      float o = __fsub_rn(__fmul_rn(k.p_x, xc), __fmul_rn(k.p_m0, x0));
+      if (k.pred_order == 2)
+        o = __fsub_rn(o, __fmul_rn(k.p_bh, __fmul_rn(0.5f, __fdiv_rn(__fsub_rn(m0a[q], x0), k.p_rk))));
+      x0a[q] = x0; xca[q] = xc; oa[q] = o;
+    }
+    reinterpret_cast<float4*>(x0_out)[i] = make_float4(x0a[0], x0a[1], x0a[2], x0a[3]);
+    reinterpret_cast<float4*>(last_out)[i] = make_float4(xca[0], xca[1], xca[2], xca[3]);
+    reinterpret_cast<uint2*>(latents_out)[i] = make_uint2(vc::pack_bf16x2(oa[0], oa[1]), vc::pack_bf16x2(oa[2], oa[3]));
+  }
+}
+
 int grid_for(long long work_items, int threads) {
   long long blocks = (work_items + threads - 1) / threads;
   const long long cap = 148LL * 8;
@@ -154,4 +222,33 @@ extern "C" int vc_cfg_euler_step(const void* pred_uncond, const void* pred_text,
       (const __nv_bfloat16*)pred_uncond, (const __nv_bfloat16*)pred_text, (const __nv_bfloat16*)latents,
       (__nv_bfloat16*)latents_out, (__nv_bfloat16*)guided_out, n / 8, guidance, dt, pred_text != nullptr ? 1 : 0);
   VC_RETURN_LAUNCH_STATUS("vc_cfg_euler_step");
+}
+
+extern "C" int vc_cfg_unipc_step(const void* pred_uncond, const void* pred_text, const void* latents, const void* last,
+                                 const void* m0, const void* m1, void* latents_out, void* x0_out, void* last_out,
+                                 long long n, float guidance, const float* coef, void* stream) {
+  VC_CHECK_ARG(pred_uncond && latents && latents_out && x0_out && last_out && coef, "vc_cfg_unipc_step: null operand");
+  VC_CHECK_ARG(n >= 0 && n % 4 == 0, "vc_cfg_unipc_step: element count must be a multiple of 4 (got %lld)", n);
+  UniPCCoef k;
+  k.sigma = coef[0];
+  k.corr_order = (int)coef[1];
+  k.c_x = coef[2]; k.c_m0 = coef[3]; k.c_bh = coef[4]; k.c_rho0 = coef[5]; k.c_rk = coef[6]; k.c_rhot = coef[7];
+  k.pred_order = (int)coef[8];
+  k.p_x = coef[9]; k.p_m0 = coef[10]; k.p_bh = coef[11]; k.p_rk = coef[12];
+  VC_CHECK_ARG(k.corr_order >= 0 && k.corr_order <= 2 && k.pred_order >= 1 && k.pred_order <= 2,
+               "vc_cfg_unipc_step: corrector order 0..2 and predictor order 1..2 (got %d, %d)", k.corr_order, k.pred_order);
+  VC_CHECK_ARG(k.corr_order == 0 || (last && m0), "vc_cfg_unipc_step: the corrector needs `last` and `m0`");
+  VC_CHECK_ARG(k.corr_order < 2 || m1, "vc_cfg_unipc_step: the order-2 corrector needs `m1`");
+  VC_CHECK_ARG(k.pred_order < 2 || k.corr_order >= 1 || m0, "vc_cfg_unipc_step: the order-2 predictor needs `m0`");
+  VC_CHECK_ARG((reinterpret_cast<uintptr_t>(pred_uncond) | reinterpret_cast<uintptr_t>(pred_text) |
+                reinterpret_cast<uintptr_t>(latents) | reinterpret_cast<uintptr_t>(latents_out)) % 8 == 0 &&
+               (reinterpret_cast<uintptr_t>(last) | reinterpret_cast<uintptr_t>(m0) | reinterpret_cast<uintptr_t>(m1) |
+                reinterpret_cast<uintptr_t>(x0_out) | reinterpret_cast<uintptr_t>(last_out)) % 16 == 0,
+               "vc_cfg_unipc_step: bf16 operands must be 8-byte and fp32 operands 16-byte aligned");
+  if (n == 0) return 0;
+  cfg_unipc_step_kernel<<<grid_for(n / 4, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)pred_uncond, (const __nv_bfloat16*)pred_text, (const __nv_bfloat16*)latents,
+      (const float*)last, (const float*)m0, (const float*)m1, (__nv_bfloat16*)latents_out, (float*)x0_out,
+      (float*)last_out, n / 4, guidance, pred_text != nullptr ? 1 : 0, k);
+  VC_RETURN_LAUNCH_STATUS("vc_cfg_unipc_step");
 }

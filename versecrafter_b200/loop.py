@@ -7,7 +7,8 @@
   * denoise(): the sampling loop of `WanVerseCrafterPipeline.__call__` (:866-909) around a drop-in transformer
     (single model or the Wan2.2 expert switch) for callers that do not bring the reference pipeline object.
 
-The VAE, the text encoder and the UniPC / DPM++ multistep schedulers stay external (VideoX-Fun / diffusers)."""
+The reference's default sampler (flow-matching UniPC) is schedulers.FlowUniPCMultistepScheduler (one fused kernel per
+step); pass it to denoise(scheduler=...).  The VAE, the text encoder and the DPM++ scheduler stay external."""
 import ctypes
 
 import torch
@@ -85,27 +86,37 @@ def flow_shift_sigmas(num_steps, shift=5.0, num_train_timesteps=1000):
 
 
 @torch.no_grad()
-def denoise(transformer, latents, geoada_ctx, context, sigmas, guidance_scale=5.0, geoada_context_scale=1.0,
-            num_train_timesteps=1000, callback=None):
-    """The denoising loop of pipeline_wan_versecrafter.py:866-909 with the Euler flow-matching scheduler.
-    latents [1, 16, F, H, W] bf16; geoada_ctx [128, F, H, W]; context = [negative, positive] text embeddings (CFG) or
-    [positive]; sigmas: N+1 descending values (flow_shift_sigmas).  Returns the final latents."""
+def denoise(transformer, latents, geoada_ctx, context, sigmas=None, guidance_scale=5.0, geoada_context_scale=1.0,
+            num_train_timesteps=1000, callback=None, scheduler=None):
+    """The denoising loop of pipeline_wan_versecrafter.py:866-909.  latents [1, 16, F, H, W] bf16; geoada_ctx
+    [128, F, H, W]; context = [negative, positive] text embeddings (CFG) or [positive].  Either `sigmas` (N+1
+    descending values, flow_shift_sigmas: Euler flow-matching updates) or `scheduler` (a
+    schedulers.FlowUniPCMultistepScheduler after set_timesteps: the reference's default sampler; the model sees its
+    integer `timesteps`, :750-752,:890).  Returns the final latents."""
     do_cfg = guidance_scale > 1.0 and len(context) == 2
     B = 2 if do_cfg else 1
     _, _, Fr, Hh, Ww = latents.shape
     ps = transformer.config.patch_size
     seq_len = -(-(Hh * Ww) // (ps[1] * ps[2])) * Fr                     # :858-862
-    n_steps = len(sigmas) - 1
+    if (sigmas is None) == (scheduler is None):
+        raise _lib.VCError("denoise: pass exactly one of `sigmas` (Euler) or `scheduler` (UniPC)")
+    n_steps = len(sigmas) - 1 if scheduler is None else len(scheduler.timesteps)
     transformer.num_inference_steps = n_steps                           # :869
     geo = [geoada_ctx] * B                                              # :883-887 (both CFG halves share the control)
     x = latents.contiguous()
     for i in range(n_steps):
         transformer.current_steps = i                                   # :872
-        t = torch.full((B,), float(sigmas[i]) * num_train_timesteps, device=x.device, dtype=torch.float32)
+        if scheduler is None:
+            t = torch.full((B,), float(sigmas[i]) * num_train_timesteps, device=x.device, dtype=torch.float32)
+        else:
+            t = scheduler.timesteps[i].to(x.device).expand(B)
         pred = transformer(x=torch.cat([x] * B) if do_cfg else x, t=t, geoada_context=geo, context=context,
                            seq_len=seq_len, geoada_context_scale=geoada_context_scale)
-        dt = float(sigmas[i + 1]) - float(sigmas[i])
-        x = cfg_euler_step(pred[0:1], pred[1:2] if do_cfg else None, x, guidance_scale, dt)
+        if scheduler is None:
+            dt = float(sigmas[i + 1]) - float(sigmas[i])
+            x = cfg_euler_step(pred[0:1], pred[1:2] if do_cfg else None, x, guidance_scale, dt)
+        else:
+            x = scheduler.step_cfg(pred[0:1], pred[1:2] if do_cfg else None, x, guidance_scale)
         if callback is not None:
             callback(i, t, x)
     return x
