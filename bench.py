@@ -236,6 +236,7 @@ def run_gpu_arm(args):
 
     model = VerseCrafterWanTransformer3DModel(**cfg, device="cuda", dtype=torch.bfloat16, init=False)
     model.synthetic_init_(seed=0)
+    model.cache_step_invariants = False   # every timed step is a full reference forward (text MLP + 60x cross K/V included)
     model.eval()
     if world > 1:
         model.enable_multi_gpus_inference()
@@ -320,7 +321,7 @@ def run_gpu_arm(args):
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": desc, "name": args.config, "tokens_per_step": tokens, "batch": B, "seq_len": L,
                        "parallelism": f"ulysses_sp{world}", "l2": "working set per kernel >> 126 MB L2 (no flush needed)",
-                       "teacache": "off", "cfg_skip": "off", "weights": "random non-trivial bf16 (synthetic_init_)"},
+                       "teacache": "off", "cfg_skip": "off", "step_cache": "off", "weights": "random non-trivial bf16 (synthetic_init_)"},
             "step_pflop": (gemm_f + attn_f) / 1e15,
             "step_frac_of_bf16_sustained": (gemm_f + attn_f) / world / (ms_step * 1e9) / peaks["bf16_tflops_sustained"],
             "roofline": roofline, "kernels": kern, "clocks": clocks,

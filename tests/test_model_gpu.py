@@ -136,3 +136,46 @@ def test_teacache_and_cfg_skip_surface():
     assert torch.equal(y_skip[0], y_skip[1]) and cosine(y_skip[1], y_full[1]) > 0.9999
     model.disable_cfg_skip()
     assert model.config.patch_size == (1, 2, 2) and len(model.blocks) == 2
+
+
+def test_step_invariant_cache_is_exact_and_invalidates():
+    """the embedded text and each block's cross-attention K|V are kept across steps.  The cached forward
+    is BIT-identical to the uncached one; an in-place change of a prompt embedding, new prompt tensors, or reloaded
+    weights drop the cache."""
+    from versecrafter_b200 import ops
+    cfg = dict(dim=256, ffn_dim=512, num_heads=2, num_layers=2, text_dim=64, geoada_in_dim=128)
+    model, sd = build(cfg, seed=11)
+    inp = restate.synth_inputs(cfg, (2, 8, 16), seed=11, device="cuda")
+    kw = dict(x=inp["x"].bfloat16(), t=inp["t"], geoada_context=inp["geoada_context"].bfloat16(),
+              seq_len=inp["seq_len"])
+    ctx = [c.clone() for c in inp["context"]]
+    model.cache_step_invariants = False
+    y_ref = model(context=ctx, **kw)
+    n0 = ops.launch_count
+    model(context=ctx, **kw)
+    launches_uncached = ops.launch_count - n0
+    model.cache_step_invariants = True
+    y1 = model(context=ctx, **kw)                     # fills the cache
+    n0 = ops.launch_count
+    y2 = model(context=ctx, **kw)                     # served from it
+    launches_cached = ops.launch_count - n0
+    assert torch.equal(y1, y_ref) and torch.equal(y2, y_ref)
+    n_blocks = len(model.blocks) + len(model.geoada_blocks)
+    assert launches_cached == launches_uncached - 2 - 2 * n_blocks      # text MLP (2 GEMMs) + per block K|V GEMM + RMSNorm
+    y3 = model(context=[c for c in ctx], **kw)        # new list, same storages: still a hit
+    assert torch.equal(y3, y_ref) and len(model._step_cache["kv"]) == n_blocks
+    # in-place edit of the prompt embedding -> recomputed, equal to an uncached run on the edited prompt
+    ctx[1].mul_(0.5)
+    y4 = model(context=ctx, **kw)
+    model.cache_step_invariants = False
+    y4_ref = model(context=ctx, **kw)
+    model.cache_step_invariants = True
+    assert torch.equal(y4, y4_ref) and not torch.equal(y4, y_ref)
+    # reloaded weights -> cache dropped
+    model(context=ctx, **kw)
+    sd2 = restate.synth_state_dict(cfg, seed=12, device="cuda", dtype=torch.bfloat16)
+    model.load_state_dict(sd2, strict=True)
+    assert model._step_cache == {}
+    y5 = model(context=ctx, **kw)
+    model.cache_step_invariants = False
+    assert torch.equal(y5, model(context=ctx, **kw)) and not torch.equal(y5, y4)
