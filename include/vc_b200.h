@@ -69,7 +69,9 @@ int vc_gemm_bf16(const void* A, long long lda, const void* W, long long ldw, voi
  *   2: one S buffer shared by both Q tiles, P in its own TMEM columns (S_j+1 overlaps softmax_j);
  *   3: 2 + split PV issue + packed fp32x2 softmax;  4 / 5: 3 + 16 / 32 of every 128 exp2 evaluated by a
  *   degree-3 polynomial on the FMA pipe instead of the MUFU (rel. error < 1e-4, below P's bf16 rounding).
- *   4 is the fastest on B200 under the power cap and is what the drop-in module uses. */
+ *   4 is the fastest on B200 under the power cap and is what the drop-in module uses for self-attention.
+ *   6: short key sequences (cross-attention to the 512 text tokens): one 128-row Q tile per CTA, 256 TMEM columns,
+ *   96 KB smem, so two CTAs share an SM and each one's prologue/epilogue hides behind the other's MMAs. */
 int vc_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, int B, int H, int Lq, int Lk,
                       int head_dim, const long long* q_strides, const long long* k_strides,
                       const long long* v_strides, const long long* o_strides, float softmax_scale, int variant,

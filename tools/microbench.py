@@ -179,6 +179,9 @@ if __name__ == "__main__":
     if "attn_c3" in which:  # the per-launch shape of the c3 step (B=2, 40 heads, 32,760 tokens)
         for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "4").split(",")]:
             bench_attn(2, 40, 32760, 32760, variant)
+    if "xattn" in which:  # cross-attention at the c3 launch shape: shared-S kernel (4) vs the short-key kernel (6)
+        for variant in (4, 6):
+            bench_attn(2, 40, 32760, 512, variant)
     if "attn" in which:
         for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "0,1").split(",")]:
             bench_attn(1, 8, 32760, 32760, variant)

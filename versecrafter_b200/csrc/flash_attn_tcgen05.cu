@@ -716,6 +716,238 @@ int launch_sa(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& t
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Variant 6 ("x1", short key sequences = cross-attention to the 512 text tokens, K7).
+// With Lk = 512 a 256-row CTA of the kernels above has only 4 K/V tiles of work (~8k tensor cycles) between a prologue
+// (barrier init, TMEM alloc, 64 KB of Q from HBM) and an epilogue (64 KB of O) that nothing overlaps: one CTA per SM
+// (224 KB smem, 512 TMEM columns) ran cross-attention at 35 % of the tensor peak.  Here a CTA is half the size —
+// ONE 128-row Q tile, S (128 cols) | O (128 cols) = 256 TMEM columns, Q + a 2-slot K/V ring = 96 KB smem, 192 threads —
+// so TWO CTAs are resident per SM and one's prologue / softmax / epilogue hides behind the other's MMAs.
+//   warp 0  TMA producer (Q, then K_0 V_0 K_1 V_1 ... alternating over the two slots)
+//   warp 1  TMEM allocator, then one thread issues S_j = Q K_j^T and O += P_j V_j (P read from TMEM over S, TS MMA)
+//   warps 2-5  softmax, thread = query row = TMEM lane (lane quarter = warp & 3)
+// No setmaxnreg here: it is a warpgroup-wide instruction and warps 0-3 of this 192-thread CTA have different roles;
+// __launch_bounds__(192, 2) already gives every thread 168 registers.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int X1_THREADS = 192;
+constexpr int X1_NSLOT = 2;
+constexpr int X1_SMEM_BYTES = TILE_BYTES + X1_NSLOT * TILE_BYTES + 256 + 1024;
+
+__global__ void __launch_bounds__(X1_THREADS, 2)
+flash_attn_x1_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                     const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sKV = smem + TILE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + X1_NSLOT * TILE_BYTES);
+  uint64_t* q_full = bars;                  // 1
+  uint64_t* kv_full = bars + 1;             // 2
+  uint64_t* kv_empty = kv_full + X1_NSLOT;  // 2
+  uint64_t* s_full = kv_empty + X1_NSLOT;   // 1
+  uint64_t* p_ready = s_full + 1;           // 1
+  uint64_t* o_full = p_ready + 1;           // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int q_blk = blockIdx.x, head = blockIdx.y, batch = blockIdx.z;
+  const int nk = (p.Lk + BKV - 1) / BKV;
+
+  if (threadIdx.x == 0) {
+    vc::mbar_init(q_full, 1);
+    for (int i = 0; i < X1_NSLOT; ++i) {
+      vc::mbar_init(&kv_full[i], 1);
+      vc::mbar_init(&kv_empty[i], 1);
+    }
+    vc::mbar_init(s_full, 1);
+    vc::mbar_init(p_ready, 128);
+    vc::mbar_init(o_full, 1);
+    vc::fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    vc::tma_prefetch_desc(&tmQ);
+    vc::tma_prefetch_desc(&tmK);
+    vc::tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1) vc::tmem_alloc(tmem_slot, 256);
+  vc::tc_fence_before();
+  __syncthreads();
+  vc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < 2) {
+    if (warp == 0) {
+      if (vc::elect_one()) {
+        vc::mbar_expect_tx(q_full, TILE_BYTES);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) vc::tma_load_4d(sQ + h * HALF_BYTES, &tmQ, q_full, h * 64, q_blk * BQ, head, batch);
+        for (int idx = 0; idx < 2 * nk; ++idx) {
+          const int slot = idx & 1;
+          const uint32_t ph = (idx >> 1) & 1;
+          vc::mbar_wait(&kv_empty[slot], ph ^ 1);
+          vc::mbar_expect_tx(&kv_full[slot], TILE_BYTES);
+          const CUtensorMap* tm = (idx & 1) ? &tmV : &tmK;
+          const int row0 = (idx >> 1) * BKV;
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            vc::tma_load_4d(sKV + slot * TILE_BYTES + h * HALF_BYTES, tm, &kv_full[slot], h * 64, row0, head, batch);
+        }
+      }
+    } else {
+      if (vc::elect_one()) {
+        constexpr uint32_t idesc_s = vc::umma_idesc_bf16(BQ, BKV, 0, 0);  // Q (K-major) x K (K-major)
+        constexpr uint32_t idesc_o = vc::umma_idesc_bf16(BQ, HD, 0, 1);   // P (TMEM) x V (MN-major)
+        const uint32_t qa = vc::smem_u32(sQ);
+        const uint32_t ka = vc::smem_u32(sKV), va = vc::smem_u32(sKV + TILE_BYTES);   // K tiles: slot 0, V tiles: slot 1
+        auto issue_s = [&]() {
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k) {
+            const uint32_t off = (k >> 2) * HALF_BYTES + (k & 3) * 32;
+            vc::umma_ss(tmem_base, vc::umma_desc_sw128(qa + off, 16, 1024), vc::umma_desc_sw128(ka + off, 16, 1024),
+                        idesc_s, k != 0 ? 1u : 0u);
+          }
+          vc::umma_commit(s_full);
+          vc::umma_commit(&kv_empty[0]);
+        };
+        vc::mbar_wait(q_full, 0);
+        vc::mbar_wait(&kv_full[0], 0);
+        vc::tc_fence_after();
+        issue_s();
+        for (int j = 0; j < nk; ++j) {
+          vc::mbar_wait(&kv_full[1], j & 1);   // V_j
+          vc::mbar_wait(p_ready, j & 1);       // P_j written over S_j
+          vc::tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < BKV / 16; ++k)
+            vc::umma_ts(tmem_base + 128, tmem_base + k * 8, vc::umma_desc_sw128(va + k * 2048, HALF_BYTES, 1024), idesc_o,
+                        (j != 0 || k != 0) ? 1u : 0u);
+          vc::umma_commit(&kv_empty[1]);
+          if (j + 1 < nk) {
+            vc::mbar_wait(&kv_full[0], (j + 1) & 1);   // K_{j+1}
+            vc::tc_fence_after();
+            issue_s();                                 // in-order after PV_j: P_j is consumed before S is overwritten
+          } else {
+            vc::umma_commit(o_full);
+          }
+        }
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_bits = static_cast<uint32_t>(quarter * 32) << 16;
+    const uint32_t s_addr = tmem_base + lane_bits;
+    const uint32_t o_addr = tmem_base + 128 + lane_bits;
+    const float sl2 = p.scale_log2;
+    float m_run = -INFINITY, l_run = 0.f;
+
+    for (int j = 0; j < nk; ++j) {
+      vc::mbar_wait(s_full, j & 1);
+      vc::tc_fence_after();
+      uint32_t s[128];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) vc::tmem_ld32(s_addr + c * 32, s + c * 32);
+      vc::tmem_ld_wait();
+      if (j == nk - 1) {
+        const int valid = p.Lk - j * BKV;
+        if (valid < BKV) {
+#pragma unroll
+          for (int i = 0; i < 128; ++i)
+            if (i >= valid) s[i] = __float_as_uint(-INFINITY);
+        }
+      }
+      float mx[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) mx[i] = __uint_as_float(s[i]);
+#pragma unroll
+      for (int i = 8; i < 128; ++i) mx[i & 7] = fmaxf(mx[i & 7], __uint_as_float(s[i]));
+      const float mt = fmaxf(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])), fmaxf(fmaxf(mx[4], mx[5]), fmaxf(mx[6], mx[7])));
+      const float m_new = fmaxf(m_run, mt);
+      const bool need = (m_new - m_run) * sl2 > RESCALE_THRESHOLD;
+      if (__any_sync(0xffffffffu, need)) {
+        const float alpha = fast_exp2((m_run - m_new) * sl2);
+        l_run *= alpha;
+        m_run = m_new;
+        if (j > 0) {   // S_j done implies PV_{j-1} done; PV_j waits for our p_ready arrival: O is idle
+#pragma unroll 1
+          for (int c = 0; c < 4; ++c) {
+            uint32_t o[32];
+            vc::tmem_ld32(o_addr + c * 32, o);
+            vc::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            vc::tmem_st32(o_addr + c * 32, o);
+          }
+          vc::tmem_st_wait();
+        }
+      }
+      const float mb = m_run * sl2;
+      float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+      for (int i = 0; i < 64; ++i) {
+        const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -mb));
+        const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -mb));
+        sum0 += p0;
+        sum1 += p1;
+        s[i] = vc::pack_bf16x2(p0, p1);
+      }
+      vc::tmem_st32(s_addr, s);
+      vc::tmem_st32(s_addr + 32, s + 32);
+      vc::tmem_st_wait();
+      l_run += sum0 + sum1;
+      vc::tc_fence_before();
+      vc::mbar_arrive(p_ready);
+    }
+
+    vc::mbar_wait(o_full, 0);
+    vc::tc_fence_after();
+    const float inv_l = 1.0f / l_run;
+    const int q_row = q_blk * BQ + row;
+    __nv_bfloat16* orow = p.O + (long long)batch * p.o_stride_b + (long long)q_row * p.o_stride_l +
+                          (long long)head * p.o_stride_h;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t o[32];
+      vc::tmem_ld32(o_addr + c * 32, o);
+      vc::tmem_ld_wait();
+      if (q_row < p.Lq) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 u;
+          u.x = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 0]) * inv_l, __uint_as_float(o[g * 8 + 1]) * inv_l);
+          u.y = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 2]) * inv_l, __uint_as_float(o[g * 8 + 3]) * inv_l);
+          u.z = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 4]) * inv_l, __uint_as_float(o[g * 8 + 5]) * inv_l);
+          u.w = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 6]) * inv_l, __uint_as_float(o[g * 8 + 7]) * inv_l);
+          *reinterpret_cast<uint4*>(orow + c * 32 + g * 8) = u;
+        }
+      }
+    }
+  }
+
+  vc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) vc::tmem_dealloc(tmem_base, 256);
+}
+
+int launch_x1(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p, int B, int H,
+              cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(flash_attn_x1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, X1_SMEM_BYTES);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(flash_attn_x1_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if (e != cudaSuccess) {
+      vc_host::set_error("vc_flash_attn_fwd: cannot configure %d B dynamic smem: %s", X1_SMEM_BYTES, cudaGetErrorString(e));
+      return (int)e;
+    }
+    attr_set = true;
+  }
+  dim3 grid((p.Lq + BQ - 1) / BQ, H, B);
+  flash_attn_x1_kernel<<<grid, X1_THREADS, X1_SMEM_BYTES, s>>>(tq, tk, tv, p);
+  return 0;
+}
+
 }  // namespace
 
 // strides are in ELEMENTS: (batch, token, head); the head_dim axis must be contiguous (stride 1), head_dim == 128.
@@ -726,7 +958,8 @@ static int attn_impl(const void* q, const void* k, const void* v, void* o, int B
   VC_CHECK_ARG(q && k && v && o && q_strides && k_strides && v_strides && o_strides, "vc_flash_attn_fwd: null pointer");
   VC_CHECK_ARG(head_dim == HD, "vc_flash_attn_fwd: head_dim %d unsupported (only 128)", head_dim);
   VC_CHECK_ARG(B > 0 && H > 0 && Lq >= 0 && Lk > 0, "vc_flash_attn_fwd: bad sizes B=%d H=%d Lq=%d Lk=%d", B, H, Lq, Lk);
-  VC_CHECK_ARG(variant >= 0 && variant <= 5, "vc_flash_attn_fwd: variant must be 0 (P in smem), 1 (P in TMEM over S) or 2 (shared S buffer)");
+  VC_CHECK_ARG(variant >= 0 && variant <= 6,
+               "vc_flash_attn_fwd: variant must be 0 (P in smem), 1 (P in TMEM over S), 2-5 (shared S buffer) or 6 (short-key x1)");
   const long long* all[4] = {q_strides, k_strides, v_strides, o_strides};
   for (int t = 0; t < 4; ++t)
     for (int i = 0; i < 3; ++i)
@@ -748,7 +981,9 @@ static int attn_impl(const void* q, const void* k, const void* v, void* o, int B
   for (int i = 0; i < 8; ++i) p.o_peer[i] = (__nv_bfloat16*)(i < n_peers ? peer_o[i] : nullptr);
   dim3 grid((Lq + 2 * BQ - 1) / (2 * BQ), H, B);
   cudaStream_t st = (cudaStream_t)stream;
+  VC_CHECK_ARG(variant != 6 || n_peers == 0, "vc_flash_attn_fwd_scatter: variant 6 has no scatter epilogue");
   switch (variant) {
+    case 6: rc = launch_x1(tq, tk, tv, p, B, H, st); break;
     case 0: rc = launch<false>(tq, tk, tv, p, grid, st); break;
     case 1: rc = launch<true>(tq, tk, tv, p, grid, st); break;
     case 2: rc = launch_sa<false, 0>(tq, tk, tv, p, grid, st); break;

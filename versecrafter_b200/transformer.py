@@ -210,6 +210,8 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         self.sp_world_size, self.sp_world_rank, self.sp_group = 1, 0, None
         self._px, self._px_failed = None, False
         self.attn_variant = int(os.environ.get("VC_ATTN_VARIANT", "4"))
+        # cross-attention (512 text keys): the two-CTAs-per-SM short-key kernel (variant 6)
+        self.xattn_variant = int(os.environ.get("VC_XATTN_VARIANT", "6"))
         self.implicit_patch_embed = os.environ.get("VC_PATCH_EMBED", "implicit") != "explicit"
         self._ws = {}
         self._rope_cache = {}
@@ -565,7 +567,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
             if sc is not None:
                 sc["kv"][id(blk)] = (ver, kv)
         ops.flash_attn(qc.view(B, Lp, H, self.d), kv[:, :D].view(B, T, H, self.d), kv[:, D:].view(B, T, H, self.d),
-                       out=attn.view(B, Lp, H, self.d), variant=self.attn_variant)
+                       out=attn.view(B, Lp, H, self.d), variant=self.xattn_variant)
         ops.gemm(attn, ca.o.weight, ca.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_RES, residual=x2d, out=x2d)
         # FFN half
         ops.ln_modulate(x2d, m[:, 3], m[:, 4], Lp, eps=self.eps, out=h)
