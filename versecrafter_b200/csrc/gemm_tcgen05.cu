@@ -9,6 +9,8 @@
 //   warps 2-5: epilogue: tcgen05.ld 32 columns at a time -> bias / GELU-tanh / gate / scale / residual -> bf16 global
 // The accumulator is double-buffered in TMEM so tile i's epilogue overlaps tile i+1's main loop.
 // Epilogue rounding points follow the reference's op-by-op bf16 arithmetic.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace {
@@ -35,14 +37,15 @@ struct GemmParams {
   long long ldr;
   float scale;
   int m_tiles, n_tiles;
+  int group_m;  // M tiles per rasterisation group (see vc_gemm_bf16)
 };
 
-__device__ __forceinline__ void tile_coords(int t, int m_tiles, int n_tiles, int& m, int& n) {
-  const int per_group = GROUP_M * n_tiles;
+__device__ __forceinline__ void tile_coords(int t, int m_tiles, int n_tiles, int group_m, int& m, int& n) {
+  const int per_group = group_m * n_tiles;
   const int g = t / per_group;
   const int r = t - g * per_group;
-  const int m0 = g * GROUP_M;
-  const int gm = min(GROUP_M, m_tiles - m0);
+  const int m0 = g * group_m;
+  const int gm = min(group_m, m_tiles - m0);
   m = m0 + r % gm;
   n = r / gm;
 }
@@ -101,7 +104,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         int m, n;
-        tile_coords(t, p.m_tiles, p.n_tiles, m, n);
+        tile_coords(t, p.m_tiles, p.n_tiles, p.group_m, m, n);
         for (int kb = 0; kb < k_blocks; ++kb) {
           vc::mbar_wait(&empty[stage], phase ^ 1);
           vc::mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
@@ -154,7 +157,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint32_t acc_phase = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       int m, n;
-      tile_coords(t, p.m_tiles, p.n_tiles, m, n);
+      tile_coords(t, p.m_tiles, p.n_tiles, p.group_m, m, n);
       vc::mbar_wait(&acc_full[acc], acc_phase);
       vc::tc_fence_after();
       const long long row = (long long)m * BM + quarter * 32 + lane;
@@ -306,6 +309,18 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   p.scale = scale;
   p.m_tiles = (int)((M + BM - 1) / BM);
   p.n_tiles = (int)((N + BN - 1) / BN);
+  // Rasterisation: tiles are visited group by group, a group = group_m M-tiles x all N-tiles (M fastest), so the A rows of
+  // a group are re-used from L2 by consecutive waves while the weight streams past once per group.  Measured on B200
+  // (ncu dram__bytes_read per launch, M=65520): the A panel only survives between waves while one wave's footprint
+  // (group_m*128*K*2 B of A + its W tiles) stays under ~45 MB — N=15360,K=5120: 5.6 GB at group_m=16, 6.2 GB at 33,
+  // 10.5 GB at 48 (and the c3 step 2.7 % slower: DRAM traffic costs power under the 1 kW cap); K=13824: 10.5-12.9 GB
+  // for group_m 8..18.  16 is kept; VC_GEMM_GROUP_M overrides it for experiments.
+  static const int group_m = []() {
+    const char* e = getenv("VC_GEMM_GROUP_M");
+    const int g = e ? atoi(e) : 0;
+    return g >= 1 && g <= 512 ? g : GROUP_M;
+  }();
+  p.group_m = group_m;
   const long long tiles = (long long)p.m_tiles * p.n_tiles;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
   cudaStream_t s = (cudaStream_t)stream;
