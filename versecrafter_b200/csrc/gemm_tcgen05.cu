@@ -20,7 +20,7 @@ constexpr int A_BYTES = BM * BK * 2;  // 16 KB
 constexpr int B_BYTES = BN * BK * 2;  // 32 KB
 constexpr int BAR_BYTES = 256;
 constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + BAR_BYTES + 1024;  // +1024 for manual alignment
-constexpr int GROUP_M = 16;
+constexpr int GROUP_M = 16, GROUP_M_TALL = 32;
 constexpr int NUM_THREADS = 192;
 
 enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16 };
@@ -38,6 +38,7 @@ struct GemmParams {
   float scale;
   int m_tiles, n_tiles;
   int group_m;  // M tiles per rasterisation group (see vc_gemm_bf16)
+  int l2_hint;  // bit 0: A loads evict_last; bit 1: W loads evict_first; bit 2: streaming C stores
 };
 
 __device__ __forceinline__ void tile_coords(int t, int m_tiles, int n_tiles, int group_m, int& m, int& n) {
@@ -102,14 +103,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (vc::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      const uint64_t pol_a = (p.l2_hint & 1) ? vc::L2_EVICT_LAST : vc::L2_EVICT_NORMAL;
+      const uint64_t pol_b = (p.l2_hint & 2) ? vc::L2_EVICT_FIRST : vc::L2_EVICT_NORMAL;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         int m, n;
         tile_coords(t, p.m_tiles, p.n_tiles, p.group_m, m, n);
         for (int kb = 0; kb < k_blocks; ++kb) {
           vc::mbar_wait(&empty[stage], phase ^ 1);
           vc::mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
-          vc::tma_load_2d(sA + stage * A_BYTES, &tmA, &full[stage], kb * BK, m * BM);
-          vc::tma_load_2d(sB + stage * B_BYTES, &tmB, &full[stage], kb * BK, n * BN);
+          vc::tma_load_2d_hint(sA + stage * A_BYTES, &tmA, &full[stage], kb * BK, m * BM, pol_a);
+          vc::tma_load_2d_hint(sB + stage * B_BYTES, &tmB, &full[stage], kb * BK, n * BN, pol_b);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -223,7 +226,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               o.y = vc::pack_bf16x2(v[2], v[3]);
               o.z = vc::pack_bf16x2(v[4], v[5]);
               o.w = vc::pack_bf16x2(v[6], v[7]);
-              *reinterpret_cast<uint4*>(crow + col) = o;
+              if (p.l2_hint & 4) __stcs(reinterpret_cast<uint4*>(crow + col), o);
+              else *reinterpret_cast<uint4*>(crow + col) = o;
             }
           }
         }
@@ -310,17 +314,22 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   p.m_tiles = (int)((M + BM - 1) / BM);
   p.n_tiles = (int)((N + BN - 1) / BN);
   // Rasterisation: tiles are visited group by group, a group = group_m M-tiles x all N-tiles (M fastest), so the A rows of
-  // a group are re-used from L2 by consecutive waves while the weight streams past once per group.  Measured on B200
-  // (ncu dram__bytes_read per launch, M=65520): the A panel only survives between waves while one wave's footprint
-  // (group_m*128*K*2 B of A + its W tiles) stays under ~45 MB — N=15360,K=5120: 5.6 GB at group_m=16, 6.2 GB at 33,
-  // 10.5 GB at 48 (and the c3 step 2.7 % slower: DRAM traffic costs power under the 1 kW cap); K=13824: 10.5-12.9 GB
-  // for group_m 8..18.  16 is kept; VC_GEMM_GROUP_M overrides it for experiments.
-  static const int group_m = []() {
+  // a group are re-used from L2 by consecutive waves while the weight streams past once per group: DRAM reads are about
+  // |A| + |W| * m_tiles / group_m as long as the A panel survives in L2 between waves.  Measured on B200 (ncu
+  // dram__bytes_read per launch, M=65520, profiles/gemm_raster_r01.json): N=15360,K=5120 reads 5.6 GB at group_m=16,
+  // 4.3 GB at 24, 6.2 GB at 33 and 10.5 GB at 48 (panel evicted; the c3 step gets 2.7 % slower: DRAM traffic costs power
+  // under the 1 kW cap).  Loading A with an L2 evict_last policy keeps the taller panel resident: 3.8 GB at group_m=32
+  // (W evict_first is harmful: it destroys the sharing of a W tile between the CTAs of one wave, 9.5 GB).  For
+  // K=13824 no height in 8..18 gets below 10.4 GB (one wave's footprint exceeds what L2 retains), 16 is kept there.
+  // VC_GEMM_GROUP_M / VC_GEMM_L2_HINT override both for experiments.
+  static const int group_m_env = []() {
     const char* e = getenv("VC_GEMM_GROUP_M");
     const int g = e ? atoi(e) : 0;
-    return g >= 1 && g <= 512 ? g : GROUP_M;
+    return g >= 1 && g <= 512 ? g : 0;
   }();
-  p.group_m = group_m;
+  static const int l2_hint = []() { const char* e = getenv("VC_GEMM_L2_HINT"); return e ? atoi(e) & 7 : 1; }();
+  p.group_m = group_m_env ? group_m_env : (K <= 8192 ? GROUP_M_TALL : GROUP_M);
+  p.l2_hint = l2_hint;
   const long long tiles = (long long)p.m_tiles * p.n_tiles;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
   cudaStream_t s = (cudaStream_t)stream;
