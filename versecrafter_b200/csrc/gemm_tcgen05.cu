@@ -20,7 +20,7 @@ constexpr int A_BYTES = BM * BK * 2;  // 16 KB
 constexpr int B_BYTES = BN * BK * 2;  // 32 KB
 constexpr int BAR_BYTES = 256;
 constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + BAR_BYTES + 1024;  // +1024 for manual alignment
-constexpr int GROUP_M = 16, GROUP_M_TALL = 32;
+constexpr int GROUP_M = 16;
 constexpr int NUM_THREADS = 192;
 
 enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16 };
@@ -320,15 +320,18 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   // 4.3 GB at 24, 6.2 GB at 33 and 10.5 GB at 48 (panel evicted; the c3 step gets 2.7 % slower: DRAM traffic costs power
   // under the 1 kW cap).  Loading A with an L2 evict_last policy keeps the taller panel resident: 3.8 GB at group_m=32
   // (W evict_first is harmful: it destroys the sharing of a W tile between the CTAs of one wave, 9.5 GB).  For
-  // K=13824 no height in 8..18 gets below 10.4 GB (one wave's footprint exceeds what L2 retains), 16 is kept there.
-  // VC_GEMM_GROUP_M / VC_GEMM_L2_HINT override both for experiments.
+  // K=13824 no height in 8..18 gets below 10.4 GB (one wave's footprint exceeds what L2 retains).
+  // A same-box A/B of the whole c3 step (two runs each, alternating) decided the default: group_m=16 without hints
+  // 4191.9 / 4198.3 ms (GEMMs 1,340 / 1,334 TFLOP/s) vs evict_last + group_m=32 4200.2 / 4208.2 ms (1,325 / 1,322):
+  // the lower DRAM traffic does not pay for itself, so the plain setting stays.  VC_GEMM_GROUP_M / VC_GEMM_L2_HINT
+  // (bit 0: A evict_last, bit 1: W evict_first, bit 2: streaming C stores) remain for experiments.
   static const int group_m_env = []() {
     const char* e = getenv("VC_GEMM_GROUP_M");
     const int g = e ? atoi(e) : 0;
     return g >= 1 && g <= 512 ? g : 0;
   }();
-  static const int l2_hint = []() { const char* e = getenv("VC_GEMM_L2_HINT"); return e ? atoi(e) & 7 : 1; }();
-  p.group_m = group_m_env ? group_m_env : (K <= 8192 ? GROUP_M_TALL : GROUP_M);
+  static const int l2_hint = []() { const char* e = getenv("VC_GEMM_L2_HINT"); return e ? atoi(e) & 7 : 0; }();
+  p.group_m = group_m_env ? group_m_env : GROUP_M;
   p.l2_hint = l2_hint;
   const long long tiles = (long long)p.m_tiles * p.n_tiles;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
