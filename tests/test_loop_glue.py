@@ -256,3 +256,65 @@ def test_denoise_loop_unipc():
     assert float(cos) > 0.9999
     with pytest.raises(Exception):
         loop.denoise(model, x0, geo, inp["context"])     # neither sigmas nor scheduler
+
+
+# ---- flow-matching DPM-Solver++ 2M ("Flow_DPM++"; upstream class un-vendored: parity unpinned) -------------------
+def test_dpm_oracle_integrates_straight_paths_exactly():
+    torch.manual_seed(1)
+    x0, n = torch.randn(1, 4, 3, 8, 8), torch.randn(1, 4, 3, 8, 8)
+    for steps, shift in ((10, 16.0), (3, 5.0), (1, 3.0)):
+        s = lr.FlowDPMSolverOracle()
+        s.set_timesteps(steps, shift=shift)
+        x = (1 - s.sigmas[0]) * x0 + s.sigmas[0] * n
+        for _ in range(steps):
+            x = s.step(n - x0, x)
+        assert float((x - x0).abs().max()) < 5e-6
+
+
+@pytest.mark.parametrize("steps,shift", [(8, 16.0), (3, 5.0), (2, 1.0), (1, 3.0)])
+def test_dpm_host_coefficients_match_oracle(steps, shift):
+    """FlowDPMSolverMultistepScheduler = the UniPC kernel with the corrector off: its per-step scalars pushed through the
+    kernel's formula follow the independently written DPM-Solver++ oracle."""
+    from versecrafter_b200 import schedulers
+    sch = schedulers.FlowDPMSolverMultistepScheduler(shift=1)
+    sch.set_timesteps(steps, shift=shift)
+    orc = lr.FlowDPMSolverOracle()
+    orc.set_timesteps(steps, shift=shift)
+    assert torch.equal(sch.timesteps, orc.timesteps) and torch.equal(sch.sigmas, orc.sigmas)
+    g = torch.Generator().manual_seed(steps + 100)
+    x = torch.randn(1, 16, 2, 6, 8, generator=g).bfloat16()
+    last = m0 = m1 = None
+    sch._state = dict(have_last=False)
+    for i in range(steps):
+        u, c = (torch.randn(x.shape, generator=g).bfloat16() for _ in range(2))
+        coef, op = sch._coefficients()
+        assert int(coef[1]) == 0                                   # never a corrector
+        out, x0, xc = _kernel_formula(coef, u, c, x, last, m0, m1, 5.0)
+        m1, m0, last = m0, x0, xc
+        sch._state["have_last"] = True
+        sch._this_order = op
+        sch._lower_order_nums = min(sch._lower_order_nums + 1, sch.solver_order)
+        sch._step_index += 1
+        want = orc.step(lr.cfg_combine(u, c, 5.0), x)
+        x = out.bfloat16()
+        d = (x.float() - want.float()).abs()
+        assert float(d.max()) <= 2 ** -7 * max(1.0, float(want.float().abs().max())) and float((d > 0).float().mean()) < 0.01
+
+
+@pytest.mark.gpu
+def test_dpm_kernel_matches_oracle():
+    from versecrafter_b200 import schedulers
+    steps, shift, shape = 6, 12.0, (1, 16, 5, 30, 52)
+    sch = schedulers.FlowDPMSolverMultistepScheduler(shift=1)
+    sch.set_timesteps(steps, device="cuda", shift=shift)
+    orc = lr.FlowDPMSolverOracle()
+    orc.set_timesteps(steps, shift=shift)
+    g = torch.Generator(device="cuda").manual_seed(41)
+    x = torch.randn(shape, generator=g, device="cuda").bfloat16()
+    for i in range(steps):
+        u, c = (torch.randn(shape, generator=g, device="cuda").bfloat16() for _ in range(2))
+        got = sch.step_cfg(u, c, x, 4.0)
+        want = orc.step(lr.cfg_combine(u, c, 4.0).cpu(), x.cpu())
+        d = (got.cpu().float() - want.float()).abs()
+        assert float(d.max()) <= 2 ** -7 * max(1.0, float(want.float().abs().max())) and float((d > 0).float().mean()) < 0.01
+        x = got

@@ -8,7 +8,8 @@
     (single model or the Wan2.2 expert switch) for callers that do not bring the reference pipeline object.
 
 The reference's default sampler (flow-matching UniPC) is schedulers.FlowUniPCMultistepScheduler (one fused kernel per
-step); pass it to denoise(scheduler=...).  The VAE, the text encoder and the DPM++ scheduler stay external."""
+step), schedulers.FlowDPMSolverMultistepScheduler the "Flow_DPM++" one; pass either to denoise(scheduler=...).
+The VAE and the text encoder stay external."""
 import ctypes
 
 import torch

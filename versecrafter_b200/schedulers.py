@@ -157,3 +157,20 @@ class FlowUniPCMultistepScheduler:
     def step(self, model_output, timestep=None, sample=None, return_dict=True, generator=None, **_ignored):
         prev = self.step_cfg(model_output.contiguous(), None, sample.contiguous())
         return (prev,) if not return_dict else {"prev_sample": prev}
+
+
+class FlowDPMSolverMultistepScheduler(FlowUniPCMultistepScheduler):
+    """The reference's "Flow_DPM++" sampler (inference/versecrafter_inference.py:38,:255;
+    `videox_fun.utils.fm_solvers.FlowDPMSolverMultistepScheduler`, un-vendored): data-prediction DPM-Solver++ 2M with the
+    midpoint rule, first-order first and last steps.  Its update is algebraically the UniPC `bh2` predictor of the
+    same order (expm1(-h) = B(h), (m1 - m0)/r_k = D1), so it runs on the same kernel with the corrector switched off on
+    every step."""
+
+    def __init__(self, *a, algorithm_type="dpmsolver++", solver_type="midpoint", **kw):
+        if algorithm_type != "dpmsolver++" or solver_type != "midpoint":
+            raise _lib.VCError("FlowDPMSolverMultistepScheduler: only dpmsolver++ / midpoint (the reference's setting)")
+        super().__init__(*a, **kw)
+
+    def set_timesteps(self, num_inference_steps, device=None, sigmas=None, mu=None, shift=None):
+        super().set_timesteps(num_inference_steps, device=device, sigmas=sigmas, mu=mu, shift=shift)
+        self.disable_corrector = list(range(self.num_inference_steps))
