@@ -135,3 +135,57 @@ def test_mesh_depth_renderer_matches_oracle():
         assert np.array_equal(mask[b].cpu().numpy(), oracle[b][1]) and oracle[b][1].sum() > 100
         assert np.array_equal(depth[b].cpu().numpy(), oracle[b][0])
     assert not mask[2].any() and (depth[2] == 0).all()
+
+
+def test_global_depth_range_matches_quantiles_and_handles_empty():
+    from versecrafter_b200 import control_maps as cm
+    g = torch.Generator().manual_seed(3)
+    a, b = torch.rand(3, 20, 30, generator=g) * 4 + 0.5, torch.zeros(2, 20, 30)
+    a[0, :5] = 0.0
+    lo, hi = cm.compute_global_depth_range([a, b])
+    v = a[a > 0]
+    assert lo == pytest.approx(float(torch.quantile(v, 0.001))) and hi == pytest.approx(float(torch.quantile(v, 0.99)))
+    assert cm.compute_global_depth_range([b]) == (0.0, 1.0)
+    lo2, hi2 = cm.compute_global_depth_range([a], max_samples=500, generator=torch.Generator().manual_seed(0))
+    assert 0.5 <= lo2 <= 0.7 and 4.2 <= hi2 <= 4.5          # subsampled, like the reference above 1 M values
+
+
+@pytest.mark.gpu
+def test_render_control_maps_chain_matches_oracle_chain():
+    """Steps 5-9 of the reference renderer's main() on the kernels == the same chain written with the oracle functions."""
+    from oracle import control_maps_restate as cr
+    from versecrafter_b200 import control_maps as cm
+    pts, col = cloud(11, 2500)
+    N = 3
+    Ts = [pose(0.02 * f, 0.0, -0.03 * f, 0.02 * f) for f in range(N)]
+    ell = [[(np.array([-0.3 + 0.05 * f, 0.05, 2.2], np.float32), np.diag([0.03, 0.02, 0.025]).astype(np.float32)),
+            (np.array([0.35, -0.1, 3.0 - 0.1 * f], np.float32), np.diag([0.02, 0.05, 0.02]).astype(np.float32))] for f in range(N)]
+    ell[2] = ell[2][:1]
+    gp = [{str(i): (torch.from_numpy(m), torch.from_numpy(c)) for i, (m, c) in enumerate(e)} for e in ell]
+    idx = {"0": 0, "1": 4}
+    out = cm.render_control_maps(torch.from_numpy(pts).cuda(), torch.from_numpy(col).cuda(), ell, gp, idx, [K] * N, Ts, (H, W),
+                                 point_size=0.06, gaussian_mask_threshold=0.01, scale_factor=2.5, subdivisions=2)
+    lo, hi = out["depth_range"]
+    for f in range(N):
+        bg_rgb, bg_depth, bg_mask = rr.render_points(pts, col, K, Ts[f], (H, W), 0.06)
+        meshes = [rr.ellipsoid_mesh(m, c, scale_factor=2.5, subdivisions=2) for m, c in ell[f]]
+        verts = np.concatenate([v for v, _ in meshes])
+        faces = np.concatenate([fc + sum(len(v) for v, _ in meshes[:i]) for i, (_, fc) in enumerate(meshes)])
+        fg_depth, fg_mask, _ = rr.render_mesh_depth(verts, faces, K, Ts[f], (H, W))
+        assert np.array_equal(out["background_RGB"][f].cpu().numpy(), bg_rgb)
+        assert np.array_equal(out["bg_depth"][f].cpu().numpy(), bg_depth) and np.array_equal(out["fg_depth"][f].cpu().numpy(), fg_depth)
+        t = torch.from_numpy
+        assert torch.equal(out["background_depth"][f].cpu(), cr.depth_to_gray(t(bg_depth), lo, hi))
+        assert torch.equal(out["3D_gaussian_depth"][f].cpu(), cr.depth_to_gray(t(fg_depth), lo, hi))
+        assert torch.equal(out["merged_mask"][f].cpu(), cr.merge_bg_and_fg_mask(t(bg_depth), t(fg_depth), t(bg_mask), t(fg_mask)))
+        g_rgb, g_alpha = cr.project_frame([(t(m), t(c)) for m, c in ell[f]], [tuple(v / 255 for v in cm.TAB20_255[idx[str(i)]]) for i in range(len(ell[f]))],
+                                          t(K), t(Ts[f]), W, H, 0.01)
+        want = cr.masked_projection(g_rgb, g_alpha)
+        diff = (out["3D_gaussian_RGB"][f].cpu().int() - want.int()).abs()
+        assert int(diff.max()) <= 1 and float((diff > 0).float().mean()) < 0.02
+    # the range is the quantile pair of all positive depths of the three stacks
+    _, comb = cm.composite_by_depth(out["background_RGB"], out["bg_depth"], torch.zeros_like(out["background_RGB"]), out["fg_depth"], out["fg_mask"])
+    assert (lo, hi) == cm.compute_global_depth_range([out["bg_depth"], out["fg_depth"], comb])
+    # no Gaussians at all -> black projection video, everything else unchanged
+    out0 = cm.render_control_maps(torch.from_numpy(pts).cuda(), torch.from_numpy(col).cuda(), [[]] * N, [], idx, [K] * N, Ts, (H, W), point_size=0.06)
+    assert int(out0["3D_gaussian_RGB"].max()) == 0 and not bool(out0["fg_mask"].any()) and torch.equal(out0["background_RGB"], out["background_RGB"])

@@ -139,3 +139,58 @@ def project_3d_gaussians_to_2d(gaussian_params_per_frame, obj_id_to_color_idx, i
                    "vc_gaussian_projection")
         ops.launch_count += 2
     return (rgb, alpha) if blend is None else (rgb, alpha, blend, masked)
+
+
+def compute_global_depth_range(depth_stacks, max_samples=1000000, generator=None):
+    """compute_global_depth_range (:541-571): 0.1 % / 99 % quantiles of all positive depths of the given frame stacks
+    (a random subset of `max_samples` values when there are more, as in the reference) -> (min_depth, max_depth) python
+    floats; (0.0, 1.0) when nothing is valid.  Plain torch on the stacks' device: a reduction over a scalar range, not a
+    per-pixel stage."""
+    vals = [d[d > 0].flatten() for d in depth_stacks if d.numel() and bool((d > 0).any())]
+    if not vals:
+        return 0.0, 1.0
+    v = torch.cat(vals)
+    if v.numel() > max_samples:
+        v = v[torch.randperm(v.numel(), device=v.device, generator=generator)[:max_samples]]
+    return float(torch.quantile(v, 0.001)), float(torch.quantile(v, 0.99))
+
+
+def render_control_maps(background_points, background_colors, ellipsoids_per_frame, gaussian_params_per_frame,
+                        obj_id_to_color_idx, intrinsics, extrinsics, image_size, point_size=0.01,
+                        gaussian_mask_threshold=0.05, depth_range=None, scale_factor=2.0, subdivisions=3):
+    """Steps 5-9 of the reference renderer's main() (:1240-1330) on this library's kernels, whole frame stacks at once:
+    background point-cloud splat, ellipsoid depth/mask, global-range depth -> gray, merged mask, 3D-Gaussian RGB
+    projection.  Returns the five control videos the VerseCrafter pipeline consumes as uint8 [N, H, W, 3] CUDA tensors
+    (names = the reference's output files) plus the intermediate depths/masks.
+      background_points fp32 [P,3], background_colors uint8 [P,3] (CUDA); ellipsoids_per_frame: per frame a list of
+      (mean[3], cov[3,3]) (may be empty); gaussian_params_per_frame: per frame {obj_id: (mean, cov)};
+      intrinsics [N,3,3], extrinsics [N,4,4]; image_size = (H, W)."""
+    from . import raster
+    H, W = image_size
+    N = len(extrinsics)
+    dev = background_points.device
+    bg_rgb, bg_depth, bg_mask = raster.render_point_cloud_batch(background_points, background_colors, intrinsics, extrinsics,
+                                                                (H, W), point_size=point_size)
+    meshes = []
+    for f in range(N):
+        parts = [raster.make_ellipsoid_mesh(m, c, scale_factor, subdivisions, device=dev) for m, c in ellipsoids_per_frame[f]]
+        meshes.append(raster.combine_meshes_for_scene(parts))
+    fg_depth, fg_mask = raster.render_meshes_depth_batch(meshes, intrinsics, extrinsics, (H, W))
+    fg_rgb = torch.zeros_like(bg_rgb)          # the shaded ellipsoid colour is discarded by the reference (:1281)
+    _, combined_depth = composite_by_depth(bg_rgb, bg_depth, fg_rgb, fg_depth, fg_mask)
+    lo, hi = depth_range if depth_range is not None else compute_global_depth_range([bg_depth, fg_depth, combined_depth])
+    out = {
+        "background_RGB": bg_rgb,
+        "background_depth": visualize_depth_as_grayscale(bg_depth, lo, hi),
+        "3D_gaussian_depth": visualize_depth_as_grayscale(fg_depth, lo, hi),
+        "merged_mask": merge_bg_and_fg_mask(bg_depth, fg_depth, bg_mask, fg_mask),
+        "depth_range": (lo, hi), "bg_depth": bg_depth, "fg_depth": fg_depth, "bg_mask": bg_mask, "fg_mask": fg_mask,
+    }
+    gp = list(gaussian_params_per_frame) + [{}] * (N - len(gaussian_params_per_frame))
+    if any(len(p) for p in gp):
+        _, _, _, masked = project_3d_gaussians_to_2d(gp, obj_id_to_color_idx, intrinsics, extrinsics, (W, H),
+                                                     threshold=gaussian_mask_threshold, device=dev, background_frames=bg_rgb)
+        out["3D_gaussian_RGB"] = masked
+    else:
+        out["3D_gaussian_RGB"] = torch.zeros_like(bg_rgb)
+    return out
