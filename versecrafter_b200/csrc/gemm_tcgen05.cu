@@ -58,7 +58,11 @@ __device__ __forceinline__ float gelu_tanh(float x) {
   return 0.5f * x * (1.0f + t);
 }
 
-template <int EPI>
+// kMC: the grid is launched as clusters of 2 CTAs that work on two vertically adjacent M tiles of the same N tile; each
+// CTA fetches its own A tile and HALF of the shared W tile, multicast into both CTAs' shared memory (L2 -> SM operand
+// traffic 32 KB instead of 48 KB per k-block and CTA).  A stage is free only when BOTH consumers have released it (their
+// tcgen05.commit arrives on both CTAs' `empty` barriers), because the peer's multicast writes into this CTA's stage.
+template <int EPI, bool kMC>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -77,7 +81,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (threadIdx.x == 0) {
     for (int i = 0; i < STAGES; ++i) {
       vc::mbar_init(&full[i], 1);
-      vc::mbar_init(&empty[i], 1);
+      vc::mbar_init(&empty[i], kMC ? 2 : 1);
     }
     for (int i = 0; i < 2; ++i) {
       vc::mbar_init(&acc_full[i], 1);
@@ -94,8 +98,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   vc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (kMC) vc::cluster_sync();  // the peer's barriers are initialised before anything is multicast to them
 
-  const int num_tiles = p.m_tiles * p.n_tiles;
+  // work items: tiles, or (kMC) pairs of M tiles handled by one cluster; both CTAs of a cluster walk the same list
+  const int crank = kMC ? (int)vc::cluster_ctarank() : 0;
+  const int t_first = kMC ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int t_step = kMC ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int sched_m = kMC ? (p.m_tiles + 1) / 2 : p.m_tiles;
+  const int sched_g = kMC ? max(p.group_m / 2, 1) : p.group_m;
+  const int num_tiles = sched_m * p.n_tiles;
   const int k_blocks = (int)((p.K + BK - 1) / BK);
 
   if (warp == 0) {
@@ -105,14 +116,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       const uint64_t pol_a = (p.l2_hint & 1) ? vc::L2_EVICT_LAST : vc::L2_EVICT_NORMAL;
       const uint64_t pol_b = (p.l2_hint & 2) ? vc::L2_EVICT_FIRST : vc::L2_EVICT_NORMAL;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int t = t_first; t < num_tiles; t += t_step) {
         int m, n;
-        tile_coords(t, p.m_tiles, p.n_tiles, p.group_m, m, n);
+        tile_coords(t, sched_m, p.n_tiles, sched_g, m, n);
+        if (kMC) m = 2 * m + crank;  // may be one past the last M tile: loads are zero-filled, stores masked
         for (int kb = 0; kb < k_blocks; ++kb) {
           vc::mbar_wait(&empty[stage], phase ^ 1);
           vc::mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
           vc::tma_load_2d_hint(sA + stage * A_BYTES, &tmA, &full[stage], kb * BK, m * BM, pol_a);
-          vc::tma_load_2d_hint(sB + stage * B_BYTES, &tmB, &full[stage], kb * BK, n * BN, pol_b);
+          if (kMC)
+            vc::tma_load_2d_mc(sB + stage * B_BYTES + crank * (B_BYTES / 2), &tmB, &full[stage], kb * BK,
+                               n * BN + crank * (BN / 2), (uint16_t)3);
+          else
+            vc::tma_load_2d_hint(sB + stage * B_BYTES, &tmB, &full[stage], kb * BK, n * BN, pol_b);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -128,7 +144,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int t = t_first; t < num_tiles; t += t_step) {
         vc::mbar_wait(&acc_empty[acc], acc_phase ^ 1);
         vc::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -142,7 +158,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             vc::umma_ss(d_tmem, vc::umma_desc_sw128(a0 + k * 32, 16, 1024), vc::umma_desc_sw128(b0 + k * 32, 16, 1024),
                         idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          vc::umma_commit(&empty[stage]);  // frees the smem stage when these MMAs retire
+          if (kMC) vc::umma_commit_mc(&empty[stage], (uint16_t)3);  // both CTAs' producers wait for both consumers
+          else vc::umma_commit(&empty[stage]);                       // frees the smem stage when these MMAs retire
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -158,9 +175,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int quarter = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    for (int t = t_first; t < num_tiles; t += t_step) {
       int m, n;
-      tile_coords(t, p.m_tiles, p.n_tiles, p.group_m, m, n);
+      tile_coords(t, sched_m, p.n_tiles, sched_g, m, n);
+        if (kMC) m = 2 * m + crank;  // may be one past the last M tile: loads are zero-filled, stores masked
       vc::mbar_wait(&acc_full[acc], acc_phase);
       vc::tc_fence_after();
       const long long row = (long long)m * BM + quarter * 32 + lane;
@@ -241,22 +259,48 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   vc::tc_fence_before();
   __syncthreads();
+  if (kMC) vc::cluster_sync();  // the peer may still multicast into this CTA's smem / arrive on its barriers
   if (warp == 2) vc::tmem_dealloc(tmem_base, 512);
 }
 
-template <int EPI>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
+template <int EPI, bool kMC>
+int launch_impl(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<EPI, kMC>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) {
       vc_host::set_error("vc_gemm_bf16: cannot set %d B dynamic smem: %s", SMEM_BYTES, cudaGetErrorString(e));
       return (int)e;
     }
     attr_set = true;
   }
-  gemm_bf16_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, s>>>(ta, tb, p);
+  if (!kMC) {
+    gemm_bf16_kernel<EPI, kMC><<<grid, NUM_THREADS, SMEM_BYTES, s>>>(ta, tb, p);
+    return 0;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = SMEM_BYTES;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<EPI, kMC>, ta, tb, p);
+  if (e != cudaSuccess) {
+    vc_host::set_error("vc_gemm_bf16: cluster launch failed: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
   return 0;
+}
+
+template <int EPI>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, bool mc, cudaStream_t s) {
+  return mc ? launch_impl<EPI, true>(ta, tb, p, grid, s) : launch_impl<EPI, false>(ta, tb, p, grid, s);
 }
 
 int sm_count() {
@@ -288,6 +332,9 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   VC_CHECK_ARG(!(epilogue & EPI_RES) || (residual && ldr % 8 == 0 && ldr >= N), "vc_gemm_bf16: residual epilogue without residual");
   if (M == 0) return 0;
 
+  // VC_GEMM_MC=1: clusters of 2 CTAs sharing the W tile by TMA multicast (see the kernel); needs >= 2 M tiles
+  static const bool mc_env = []() { const char* e = getenv("VC_GEMM_MC"); return e && e[0] == '1'; }();
+  const bool mc = mc_env && M > BM;
   CUtensorMap ta, tb;
   {
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
@@ -299,7 +346,7 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   {
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)N};
     uint64_t strides[1] = {(uint64_t)ldw * 2};
-    uint32_t box[2] = {BK, BN};
+    uint32_t box[2] = {BK, (uint32_t)(mc ? BN / 2 : BN)};  // multicast: each CTA of a pair fetches half of the W tile
     int rc = vc_host::make_tmap_bf16(&tb, W, 2, dims, strides, box);
     if (rc) return rc;
   }
@@ -334,16 +381,21 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   p.group_m = group_m_env ? group_m_env : GROUP_M;
   p.l2_hint = l2_hint;
   const long long tiles = (long long)p.m_tiles * p.n_tiles;
-  const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+  int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+  if (mc) {
+    const long long pairs = (long long)((p.m_tiles + 1) / 2) * p.n_tiles;
+    const int max_clusters = sm_count() / 2;
+    grid = 2 * (int)(pairs < max_clusters ? pairs : max_clusters);
+  }
   cudaStream_t s = (cudaStream_t)stream;
   int rc;
   switch (epilogue) {
-    case 0: rc = launch<0>(ta, tb, p, grid, s); break;
-    case EPI_BIAS: rc = launch<EPI_BIAS>(ta, tb, p, grid, s); break;
-    case EPI_BIAS | EPI_GELU: rc = launch<EPI_BIAS | EPI_GELU>(ta, tb, p, grid, s); break;
-    case EPI_BIAS | EPI_RES: rc = launch<EPI_BIAS | EPI_RES>(ta, tb, p, grid, s); break;
-    case EPI_BIAS | EPI_GATE | EPI_RES: rc = launch<EPI_BIAS | EPI_GATE | EPI_RES>(ta, tb, p, grid, s); break;
-    case EPI_BIAS | EPI_SCALE | EPI_RES: rc = launch<EPI_BIAS | EPI_SCALE | EPI_RES>(ta, tb, p, grid, s); break;
+    case 0: rc = launch<0>(ta, tb, p, grid, mc, s); break;
+    case EPI_BIAS: rc = launch<EPI_BIAS>(ta, tb, p, grid, mc, s); break;
+    case EPI_BIAS | EPI_GELU: rc = launch<EPI_BIAS | EPI_GELU>(ta, tb, p, grid, mc, s); break;
+    case EPI_BIAS | EPI_RES: rc = launch<EPI_BIAS | EPI_RES>(ta, tb, p, grid, mc, s); break;
+    case EPI_BIAS | EPI_GATE | EPI_RES: rc = launch<EPI_BIAS | EPI_GATE | EPI_RES>(ta, tb, p, grid, mc, s); break;
+    case EPI_BIAS | EPI_SCALE | EPI_RES: rc = launch<EPI_BIAS | EPI_SCALE | EPI_RES>(ta, tb, p, grid, mc, s); break;
     default:
       vc_host::set_error("vc_gemm_bf16: unsupported epilogue mask %d", epilogue);
       return -1;
