@@ -167,6 +167,19 @@ def test_gemm_epilogues(ops, epi):
     assert relerr(out, ref) < 4e-3
 
 
+@pytest.mark.parametrize("M,N,K", [(650, 768, 512), (129, 256, 64), (1950, 1536, 2048), (4096, 5120, 512)])
+@pytest.mark.parametrize("epi", [1, 3, 13])
+def test_gemm_multicast_schedule_is_bit_identical(ops, M, N, K, epi):
+    """The cluster-of-2 TMA-multicast schedule (odd and even M-tile counts, N tails) gives the plain kernel's bits."""
+    a, w, b = _rand((M, K), 31), _rand((N, K), 32, 1 / math.sqrt(K)), _rand((N,), 33, 0.1)
+    gate, res = _rand((2, N), 34, 0.5), _rand((M, N), 35)
+    kw = dict(gate=gate if epi & 4 else None, rows_per_batch=(M + 1) // 2, residual=res if epi & 8 else None)
+    plain = ops.gemm(a, w, b, epilogue=epi, **kw)
+    mc = ops.gemm(a, w, b, epilogue=epi | ops.SCHED_MULTICAST, **kw)
+    assert torch.equal(plain, mc)
+    assert relerr(mc, _gemm_ref(a, w, b, epi, gate, (M + 1) // 2, res, 1.0)) < 4e-3
+
+
 def test_gemm_inplace_residual_and_strided_views(ops):
     """x += scale * (c W^T + b) written over x (adapter accumulate) and A given as a column slice of a wider buffer."""
     M, N, K = 500, 512, 256

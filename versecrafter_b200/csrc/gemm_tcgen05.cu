@@ -23,7 +23,7 @@ constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + BAR_BYTES + 1024;  // 
 constexpr int GROUP_M = 16;
 constexpr int NUM_THREADS = 192;
 
-enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16 };
+enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16, SCHED_MULTICAST = 64 };
 
 struct GemmParams {
   long long M, N, K;
@@ -332,9 +332,10 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   VC_CHECK_ARG(!(epilogue & EPI_RES) || (residual && ldr % 8 == 0 && ldr >= N), "vc_gemm_bf16: residual epilogue without residual");
   if (M == 0) return 0;
 
-  // VC_GEMM_MC=1: clusters of 2 CTAs sharing the W tile by TMA multicast (see the kernel); needs >= 2 M tiles
+  // VC_GEMM_MC=1 or the VC_GEMM_SCHED_MULTICAST bit: clusters of 2 CTAs sharing the W tile by TMA multicast (see the
+  // kernel); needs >= 2 M tiles.  Same arithmetic, bit-identical results.
   static const bool mc_env = []() { const char* e = getenv("VC_GEMM_MC"); return e && e[0] == '1'; }();
-  const bool mc = mc_env && M > BM;
+  const bool mc = (mc_env || (epilogue & SCHED_MULTICAST)) && M > BM;
   CUtensorMap ta, tb;
   {
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
@@ -389,7 +390,7 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   }
   cudaStream_t s = (cudaStream_t)stream;
   int rc;
-  switch (epilogue) {
+  switch (epilogue & ~SCHED_MULTICAST) {
     case 0: rc = launch<0>(ta, tb, p, grid, mc, s); break;
     case EPI_BIAS: rc = launch<EPI_BIAS>(ta, tb, p, grid, mc, s); break;
     case EPI_BIAS | EPI_GELU: rc = launch<EPI_BIAS | EPI_GELU>(ta, tb, p, grid, mc, s); break;

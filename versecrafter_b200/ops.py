@@ -8,6 +8,7 @@ import torch
 from . import _lib
 
 EPI_BIAS, EPI_GELU, EPI_GATE, EPI_RES, EPI_SCALE = 1, 2, 4, 8, 16
+SCHED_MULTICAST = 64   # schedule bit of vc_gemm_bf16: cluster-of-2 TMA-multicast variant (same arithmetic)
 
 # kernels launched through this module since the last reset (bench.py reports it as gpu_launches)
 launch_count = 0
