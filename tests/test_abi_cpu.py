@@ -37,6 +37,18 @@ def test_version_and_arch(lib):
 def test_argument_errors_do_not_need_a_gpu(lib):
     rc = lib.vc_gemm_bf16(None, 8, None, 8, None, 8, 1, 8, 8, 0, None, None, 0, 0, None, 0, 1.0, None)
     assert rc < 0 and b"null" in lib.vc_last_error()
+    # A overlapping C is rejected (the persistent kernel re-reads A rows after C tiles of those rows are stored) ...
+    P = ctypes.c_void_p
+    rc = lib.vc_gemm_bf16(P(4096), 512, P(1 << 30), 512, P(4096), 512, 300, 512, 512, 0, None, None, 0, 0, None, 0, 1.0, None)
+    assert rc < 0 and b"overlap" in lib.vc_last_error()
+    rc = lib.vc_gemm_bf16(P(4096), 512, P(1 << 30), 512, P(4096 + 600 * 2), 1024, 300, 512, 512, 0, None, None, 0, 0, None, 0, 1.0, None)
+    assert rc < 0 and b"overlap" in lib.vc_last_error()
+    # ... but disjoint column blocks of one row-strided buffer (A = buf[:, :512], C = buf[:, 512:1024]) are not
+    # (fake addresses: only where no device exists, so the call stops at the tensor-map encoding instead of launching)
+    if not torch.cuda.is_available():
+        rc = lib.vc_gemm_bf16(P(4096), 1536, P(1 << 30), 512, P(4096 + 1024), 1536, 300, 512, 512, 0, None, None, 0, 0, None, 0,
+                              1.0, None)
+        assert rc != 0 and b"overlap" not in lib.vc_last_error()
     rc = lib.vc_ln_modulate(ctypes.c_void_p(16), 12, ctypes.c_void_p(16), 12, ctypes.c_void_p(16), ctypes.c_void_p(16), 0, 4, 4,
                             12, 1e-6, 0, None)
     assert rc < 0 and b"multiple of 8" in lib.vc_last_error()

@@ -130,3 +130,29 @@ def test_one_block_at_c3_width_and_length():
     ang = restate.rope_angles(128, GRID3, device="cuda")
     want = restate.dit_block(sd, "blocks.0.", x, e0, ang, ctx, H3)
     assert relerr(got, want) <= 1e-2
+
+
+def test_before_proj_nonzero_at_c3_width_many_waves():
+    """GeoAdapter block 0 input c = before_proj(embed(control)) + x0 with NON-ZERO before_proj at D=5120 and 32,760 rows
+    (256 M tiles x 20 N tiles = 35 waves on 148 SMs).  Round 1 ran this GEMM with out == A, which races at this size
+     and was invisible at the toy widths the model tests use."""
+    from versecrafter_b200.transformer import VerseCrafterWanTransformer3DModel
+    cfg = dict(dim=D3, ffn_dim=1024, num_heads=H3, num_layers=1, text_dim=64, geoada_in_dim=128)
+    model = VerseCrafterWanTransformer3DModel(**cfg, device="cuda", dtype=torch.bfloat16, init=False).synthetic_init_(5)
+    sd = model.state_dict()
+    lat = (21, 60, 104)
+    x, geo = _rand((1, 16) + lat, 50), _rand((1, 128) + lat, 51)
+    ctxs = [_rand((40, 64), 52, 0.1)]
+    model.record = {}
+    model(x, torch.full((1,), 500.0, device="cuda"), geo, ctxs, L3)
+    rec, model.record = model.record, None
+    x0 = restate.patch_embed(x[0], sd["patch_embedding.weight"], sd["patch_embedding.bias"], L3)
+    c0 = restate.patch_embed(geo[0], sd["geoada_patch_embedding.weight"], sd["geoada_patch_embedding.bias"], L3)
+    want = restate.linear(c0, sd["geoada_blocks.0.before_proj.weight"], sd["geoada_blocks.0.before_proj.bias"]) + x0
+    assert relerr(rec["x0"], x0) < 4e-3
+    got = rec["geo_in.0"]
+    assert relerr(got, want) < 6e-3
+    # no row block may be off (a race corrupts whole 128-row x 256-column tiles): worst 128-row block
+    blk = ((got.float() - want.float()).pow(2).sum(-1)[0, :L3 // 128 * 128].view(-1, 128).sum(1) /
+           want.float().pow(2).sum(-1)[0, :L3 // 128 * 128].view(-1, 128).sum(1)).sqrt()
+    assert float(blk.max()) < 1e-2, float(blk.max())

@@ -253,13 +253,16 @@ def test_flash_attn_large_scores_rescale(ops):
         assert relerr(ops.flash_attn(q, k, v, variant=variant), restate.sdpa(q, k, v)) < 1e-2, variant
 
 
-@pytest.mark.parametrize("P", [2, 4, 8])
-def test_ulysses_fused_kernels_emulated_ranks(ops, P):
+@pytest.mark.parametrize("P,H,grid", [(2, 16, (2, 8, 24)), (4, 16, (2, 8, 24)), (8, 16, (2, 8, 24)),
+                                      (8, 40, (3, 13, 40)),    # c3's head split (5 heads per rank), Lp = 195: ragged
+                                      (4, 40, (5, 6, 13))])    # Q tiles and a token scatter that splits inside a tile
+def test_ulysses_fused_kernels_emulated_ranks(ops, P, H, grid):
     """The fused Ulysses kernels with the P ranks emulated on ONE GPU (the "peer" buffers are P local tensors): the
     head-scatter inside RMSNorm+RoPE and the token-scatter inside the attention epilogue must reproduce, bit for bit,
     the un-sharded kernels' results sliced the way the all-to-alls would slice them."""
-    B, H, d, grid = 2, 16, 128, (2, 8, 24)
+    B, d = 2, 128
     D, L = H * d, grid[0] * grid[1] * grid[2]
+    assert L % P == 0
     Lp, Hp = L // P, H // P
     full = _rand((B, L, 3 * D), 40)
     gq = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
@@ -285,6 +288,27 @@ def test_ulysses_fused_kernels_emulated_ranks(ops, P):
                                (Lp * D, D, d), variant=4)
     for r in range(P):
         assert torch.equal(attn[r], o_ref[:, r * Lp:(r + 1) * Lp]), r
+    # zero-padded tail tokens (seq_len > F*H'*W' or L % P != 0) are not attended: keys sliced to the true length
+    Lk = L - 5
+    o_cut = ops.flash_attn(q_ref, k_ref[:, :Lk], v_ref[:, :Lk], variant=4)
+    for p in range(P):
+        ops.flash_attn_scatter(recv[p][0], recv[p][1][:, :Lk], recv[p][2][:, :Lk],
+                               [t.data_ptr() + p * Hp * d * 2 for t in attn], Lp, (Lp * D, D, d), variant=4)
+    for r in range(P):
+        assert torch.equal(attn[r], o_cut[:, r * Lp:(r + 1) * Lp]), r
+
+
+def test_gemm_rejects_output_over_its_own_input(ops):
+    """The persistent kernel re-reads A rows after C tiles of those rows are stored: A aliasing C is an argument error
+    (before_proj wrote over its input); disjoint column blocks of one buffer are allowed."""
+    from versecrafter_b200._lib import VCError
+    a, w = _rand((512, 512), 50), _rand((512, 512), 51, 1 / math.sqrt(512))
+    with pytest.raises(VCError, match="overlap"):
+        ops.gemm(a, w, None, out=a)
+    wide = _rand((512, 1024), 52)
+    want = _gemm_ref(wide[:, :512].contiguous(), w, None, 0)
+    ops.gemm(wide[:, :512], w, None, out=wide[:, 512:])
+    assert relerr(wide[:, 512:], want) < 4e-3
 
 
 def test_patchify_unpatchify(ops):

@@ -179,3 +179,30 @@ def test_step_invariant_cache_is_exact_and_invalidates():
     y5 = model(context=ctx, **kw)
     model.cache_step_invariants = False
     assert torch.equal(y5, model(context=ctx, **kw)) and not torch.equal(y5, y4)
+
+
+def test_step_cache_sees_edits_through_the_reference_named_parameters():
+    """cross_attn.k / .v are views of the packed K|V weight with their own version counters; an
+    in-place edit through them between two steps must drop that block's cached K|V."""
+    cfg = dict(dim=256, ffn_dim=512, num_heads=2, num_layers=2, text_dim=64, geoada_in_dim=128)
+    model, sd = build(cfg, seed=13)
+    inp = restate.synth_inputs(cfg, (2, 8, 16), seed=13, device="cuda")
+    kw = dict(x=inp["x"].bfloat16(), t=inp["t"], geoada_context=inp["geoada_context"].bfloat16(),
+              context=inp["context"], seq_len=inp["seq_len"])
+    model.cache_step_invariants = True
+    y0 = model(**kw)
+    y0b = model(**kw)
+    assert torch.equal(y0, y0b)
+    with torch.no_grad():
+        model.blocks[1].cross_attn.k.weight.mul_(0.5)          # in place, through the reference's parameter name
+    y1 = model(**kw)
+    model.cache_step_invariants = False
+    y1_ref = model(**kw)
+    assert torch.equal(y1, y1_ref) and not torch.equal(y1, y0)
+    model.cache_step_invariants = True
+    model(**kw)
+    model.geoada_blocks[0].cross_attn.v.bias.data += 0.25    # .data edit: invisible to version counters -> explicit call
+    model.invalidate_step_cache()
+    y2 = model(**kw)
+    model.cache_step_invariants = False
+    assert torch.equal(y2, model(**kw)) and not torch.equal(y2, y1)

@@ -32,6 +32,17 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+int sm_count() {
+  static int n[kMaxDevices] = {};
+  const int dev = current_device();
+  if (n[dev] == 0) {
+    int v = 0;
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    n[dev] = v > 0 ? v : 148;
+  }
+  return n[dev];
+}
+
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box) {
   return make_tmap(out, base, TMAP_BF16, TMAP_SWIZZLE_128B, rank, dims, strides_bytes, box);

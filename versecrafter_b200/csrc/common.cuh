@@ -245,6 +245,34 @@ int make_tmap(CUtensorMap* out, const void* base, TmapDtype dtype, TmapSwizzle s
               const uint64_t* strides_bytes, const uint32_t* box);
 }  // namespace vc_host
 
+// Per-device launch state.  cudaFuncSetAttribute and the SM count belong to the CURRENT device, so the "already done"
+// flags are kept per device ordinal (a process may drive several GPUs through this library).
+namespace vc_host {
+constexpr int kMaxDevices = 64;
+inline int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev >= 0 && dev < kMaxDevices ? dev : 0;
+}
+int sm_count();  // multiprocessors of the current device (cached per device)
+}  // namespace vc_host
+
+// Opt in to `bytes` of dynamic shared memory for `kernel` on the current device (once per device and call site; `bytes`
+// may grow between calls).  Wrap a template-id kernel in parentheses.
+#define VC_ENSURE_DYN_SMEM(kernel, bytes, what)                                                                      \
+  do {                                                                                                               \
+    static int done__[vc_host::kMaxDevices] = {};                                                                    \
+    const int dev__ = vc_host::current_device();                                                                     \
+    if (done__[dev__] < (int)(bytes)) {                                                                              \
+      cudaError_t e__ = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes));     \
+      if (e__ != cudaSuccess) {                                                                                      \
+        vc_host::set_error("%s: cannot set %d B dynamic smem: %s", what, (int)(bytes), cudaGetErrorString(e__));     \
+        return (int)e__;                                                                                             \
+      }                                                                                                              \
+      done__[dev__] = (int)(bytes);                                                                                  \
+    }                                                                                                                \
+  } while (0)
+
 #define VC_CHECK_ARG(cond, ...)        \
   do {                                 \
     if (!(cond)) {                     \

@@ -359,16 +359,8 @@ int make_qkv_map(CUtensorMap* tm, const void* base, int B, int H, int L, long lo
 template <bool kPInTmem>
 int launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p, dim3 grid,
            cudaStream_t s) {
-  static bool attr_set = false;
   constexpr int smem = Cfg<kPInTmem>::SMEM_BYTES;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(flash_attn_kernel<kPInTmem>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) {
-      vc_host::set_error("vc_flash_attn_fwd: cannot set %d B dynamic smem: %s", smem, cudaGetErrorString(e));
-      return (int)e;
-    }
-    attr_set = true;
-  }
+  VC_ENSURE_DYN_SMEM((flash_attn_kernel<kPInTmem>), smem, "vc_flash_attn_fwd");
   flash_attn_kernel<kPInTmem><<<grid, NUM_THREADS, smem, s>>>(tq, tk, tv, p);
   return 0;
 }
@@ -703,15 +695,7 @@ flash_attn_sa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 template <bool kTuned, int kPoly>
 int launch_sa(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p, dim3 grid,
               cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(flash_attn_sa_kernel<kTuned, kPoly>, cudaFuncAttributeMaxDynamicSharedMemorySize, SA_SMEM_BYTES);
-    if (e != cudaSuccess) {
-      vc_host::set_error("vc_flash_attn_fwd: cannot set %d B dynamic smem: %s", SA_SMEM_BYTES, cudaGetErrorString(e));
-      return (int)e;
-    }
-    attr_set = true;
-  }
+  VC_ENSURE_DYN_SMEM((flash_attn_sa_kernel<kTuned, kPoly>), SA_SMEM_BYTES, "vc_flash_attn_fwd");
   flash_attn_sa_kernel<kTuned, kPoly><<<grid, NUM_THREADS, SA_SMEM_BYTES, s>>>(tq, tk, tv, p);
   return 0;
 }
@@ -932,16 +916,18 @@ flash_attn_x1_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 
 int launch_x1(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p, int B, int H,
               cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(flash_attn_x1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, X1_SMEM_BYTES);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(flash_attn_x1_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-    if (e != cudaSuccess) {
-      vc_host::set_error("vc_flash_attn_fwd: cannot configure %d B dynamic smem: %s", X1_SMEM_BYTES, cudaGetErrorString(e));
-      return (int)e;
+  VC_ENSURE_DYN_SMEM(flash_attn_x1_kernel, X1_SMEM_BYTES, "vc_flash_attn_fwd");
+  {
+    static bool carve[vc_host::kMaxDevices] = {};
+    const int dev = vc_host::current_device();
+    if (!carve[dev]) {  // two CTAs of 96 KB per SM need the full shared-memory carve-out
+      cudaError_t e = cudaFuncSetAttribute(flash_attn_x1_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+      if (e != cudaSuccess) {
+        vc_host::set_error("vc_flash_attn_fwd: cannot set the shared-memory carve-out: %s", cudaGetErrorString(e));
+        return (int)e;
+      }
+      carve[dev] = true;
     }
-    attr_set = true;
   }
   dim3 grid((p.Lq + BQ - 1) / BQ, H, B);
   flash_attn_x1_kernel<<<grid, X1_THREADS, X1_SMEM_BYTES, s>>>(tq, tk, tv, p);

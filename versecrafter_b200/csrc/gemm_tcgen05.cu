@@ -265,15 +265,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
 template <int EPI, bool kMC>
 int launch_impl(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<EPI, kMC>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-    if (e != cudaSuccess) {
-      vc_host::set_error("vc_gemm_bf16: cannot set %d B dynamic smem: %s", SMEM_BYTES, cudaGetErrorString(e));
-      return (int)e;
-    }
-    attr_set = true;
-  }
+  VC_ENSURE_DYN_SMEM((gemm_bf16_kernel<EPI, kMC>), SMEM_BYTES, "vc_gemm_bf16");
   if (!kMC) {
     gemm_bf16_kernel<EPI, kMC><<<grid, NUM_THREADS, SMEM_BYTES, s>>>(ta, tb, p);
     return 0;
@@ -303,16 +295,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, in
   return mc ? launch_impl<EPI, true>(ta, tb, p, grid, s) : launch_impl<EPI, false>(ta, tb, p, grid, s);
 }
 
-int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
+using vc_host::sm_count;
 
 }  // namespace
 
@@ -331,6 +314,24 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   VC_CHECK_ARG(!(epilogue & EPI_GATE) || (gate && rows_per_batch > 0), "vc_gemm_bf16: gate epilogue without gate");
   VC_CHECK_ARG(!(epilogue & EPI_RES) || (residual && ldr % 8 == 0 && ldr >= N), "vc_gemm_bf16: residual epilogue without residual");
   if (M == 0) return 0;
+  {
+    // The kernel is persistent and multi-tile: tile (m, n) stores its C block while other CTAs / later waves still load
+    // A[m rows, 0:K] for the other N tiles, so A must not overlap C (only `residual` may alias C: each element is read
+    // and written by the same thread).  Interleaved column blocks of one row-strided buffer (same ld, disjoint
+    // columns) are fine.
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(A), c0 = reinterpret_cast<uintptr_t>(C);
+    const uintptr_t a1 = a0 + (uintptr_t)((M - 1) * lda + K) * 2, c1 = c0 + (uintptr_t)((M - 1) * ldc + N) * 2;
+    bool clash = a0 < c1 && c0 < a1;
+    if (clash && lda == ldc) {
+      const uintptr_t row_bytes = (uintptr_t)lda * 2;
+      const uintptr_t lo = a0 < c0 ? a0 : c0;
+      const uintptr_t ca = (a0 - lo) % row_bytes, cc = (c0 - lo) % row_bytes;  // column offsets within a row
+      const bool a_fits = ca + (uintptr_t)K * 2 <= row_bytes, c_fits = cc + (uintptr_t)N * 2 <= row_bytes;
+      if (a_fits && c_fits && (ca + (uintptr_t)K * 2 <= cc || cc + (uintptr_t)N * 2 <= ca)) clash = false;
+    }
+    VC_CHECK_ARG(!clash, "vc_gemm_bf16: A and C overlap (the persistent kernel re-reads A rows after C tiles of the same "
+                         "rows are stored); write C to a separate buffer");
+  }
 
   // VC_GEMM_MC=1 or the VC_GEMM_SCHED_MULTICAST bit: clusters of 2 CTAs sharing the W tile by TMA multicast (see the
   // kernel); needs >= 2 M tiles.  Same arithmetic, bit-identical results.

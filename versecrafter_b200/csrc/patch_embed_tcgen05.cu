@@ -288,12 +288,7 @@ extern "C" int vc_patch_embed(const void* x, int C, int F, int H, int W, const v
   p.N = D; p.k_blocks = 4 * C / BK; p.n_tiles = (D + BN - 1) / BN;
   // N tiles are split over blockIdx.y when that fills the 148 SMs' waves better (cost model: one transform prologue
   // ~1.5 N-tile times per CTA, one CTA per SM)
-  int sms = 148;
-  {
-    int dev = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (sms <= 0) sms = 148;
-  }
+  const int sms = vc_host::sm_count();
   int best_split = 1;
   double best_cost = 1e30;
   for (int split = 1; split <= 4 && split <= p.n_tiles; split *= 2) {
@@ -308,15 +303,7 @@ extern "C" int vc_patch_embed(const void* x, int C, int F, int H, int W, const v
   p.n_per_cta = (p.n_tiles + best_split - 1) / best_split;
   const int n_groups = (p.n_tiles + p.n_per_cta - 1) / p.n_per_cta;
   const int smem_bytes = p.k_blocks * A_BYTES + (W_STAGES - 1) * W_BYTES + RAW_STAGES * RAW_BYTES + BAR_BYTES + 1024;
-  static int attr_set = 0;
-  if (attr_set < smem_bytes) {
-    cudaError_t e = cudaFuncSetAttribute(patch_embed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-    if (e != cudaSuccess) {
-      vc_host::set_error("vc_patch_embed: cannot set %d B dynamic smem: %s", smem_bytes, cudaGetErrorString(e));
-      return (int)e;
-    }
-    attr_set = smem_bytes;
-  }
+  VC_ENSURE_DYN_SMEM(patch_embed_kernel, smem_bytes, "vc_patch_embed");
   patch_embed_kernel<<<dim3(m_tiles, n_groups), NUM_THREADS, smem_bytes, (cudaStream_t)stream>>>(tx, tw, p);
   VC_RETURN_LAUNCH_STATUS("vc_patch_embed");
 }

@@ -40,11 +40,14 @@ def all_gather_tokens(x, dim, group=None):
     return torch.cat(parts, dim=dim)
 
 
-def ulysses_attention(qkv, out, B, Lp, H, d, P, group, buf, variant=0):
-    """qkv [B*Lp, 3*H*d] (q,k already normalised + rotated with GLOBAL positions) -> out [B*Lp, H*d]."""
+def ulysses_attention(qkv, out, B, Lp, H, d, P, group, buf, variant=0, k_true=None):
+    """qkv [B*Lp, 3*H*d] (q,k already normalised + rotated with GLOBAL positions) -> out [B*Lp, H*d].
+    k_true: number of real tokens (zero-padded tail rows past it are not attended, as on one GPU)."""
     from . import ops
     D = H * d
     q, k, v = (scatter_heads(qkv[:, i * D:(i + 1) * D].reshape(B, Lp, H, d), P, group) for i in range(3))
+    if k_true is not None and k_true < P * Lp:
+        k, v = k[:, :k_true], v[:, :k_true]
     o = ops.flash_attn(q, k, v, variant=variant)
     out.view(B, Lp, H, d).copy_(gather_heads(o, P, group))
     return out
@@ -96,7 +99,7 @@ def attn_layout_index(b, t, h, rows_per_peer, n_heads, head_dim):
     return peer, ((b * rows_per_peer + tl) * n_heads + h) * head_dim
 
 
-def ulysses_attention_fused(px, qkv, B, Lp, H, d, gain_q, gain_k, rope, grid, eps, variant):
+def ulysses_attention_fused(px, qkv, B, Lp, H, d, gain_q, gain_k, rope, grid, eps, variant, k_true=None):
     """qkv [B*Lp, 3*H*d] straight from the fused QKV GEMM (NOT yet normalised) -> attention output [B*Lp, H*d] (a view
     of this rank's symmetric buffer).  Two kernels, two barriers, no NCCL call and no layout copy:
       1. RMSNorm+RoPE(q,k) | v  -> stored head-scattered into every peer's [3, B, L, H/P, d] buffer (all-to-all #1-3)
@@ -112,6 +115,8 @@ def ulysses_attention_fused(px, qkv, B, Lp, H, d, gain_q, gain_k, rope, grid, ep
     px.barrier()  # every peer's q/k/v slices have landed here; peers are done reading attn_recv of the previous block
     r = recv_t[:n_recv].view(3, B, L, Hp, d)
     head_off = rank * Hp * d * 2  # bytes: this rank's heads inside a peer's [.., H, d] row
-    ops.flash_attn_scatter(r[0], r[1], r[2], [p + head_off for p in attn_ptrs], Lp, (Lp * D, D, d), variant=variant)
+    Lk = L if k_true is None else min(k_true, L)  # padded tail tokens are not attended (k_lens, as on one GPU)
+    ops.flash_attn_scatter(r[0], r[1][:, :Lk], r[2][:, :Lk], [p + head_off for p in attn_ptrs], Lp, (Lp * D, D, d),
+                           variant=variant)
     px.barrier()  # every peer's head slices of my tokens have landed; peers are done reading their qkv_recv
     return attn_t[:n_attn].view(B * Lp, D)

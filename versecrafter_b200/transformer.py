@@ -286,6 +286,12 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         self._step_cache = {}
         self._weights_epoch = getattr(self, "_weights_epoch", 0) + 1
 
+    def invalidate_step_cache(self):
+        """Drop the step-invariant cache (embedded text, per-block cross-attention K|V).  In-place edits through the
+        parameters, load_state_dict() and .to() are detected automatically; call this after edits the version
+        counters cannot see (`weight.data += ...`, writes through raw pointers)."""
+        self._invalidate_step_cache()
+
     def load_state_dict(self, *a, **kw):
         self._invalidate_step_cache()
         return super().load_state_dict(*a, **kw)
@@ -525,7 +531,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         if self.sp_world_size > 1 and self._peer_exchange() is not None:
             # Ulysses with both all-to-alls fused into the producer kernels' stores over NVLink (sp.py)
             attn_sa = sp.ulysses_attention_fused(self._peer_exchange(), qkv, B, Lp, H, self.d, sa.norm_q.weight, sa.norm_k.weight,
-                                                 st.rope, st.grid, self.eps, max(self.attn_variant, 2))
+                                                 st.rope, st.grid, self.eps, max(self.attn_variant, 2), k_true=st.l_true)
             ops.gemm(attn_sa, sa.o.weight, sa.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_GATE | ops.EPI_RES, gate=m[:, 2],
                      rows_per_batch=Lp, residual=x2d, out=x2d)
             return self._block_tail(blk, x2d, m, ctx, st, h, attn)
@@ -538,7 +544,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
             ops.flash_attn(q4, k4, v4, out=attn.view(B, Lp, H, self.d), variant=self.attn_variant)
         else:
             sp.ulysses_attention(qkv, attn, B, Lp, H, self.d, self.sp_world_size, self.sp_group, self._buf,
-                                 variant=self.attn_variant)
+                                 variant=self.attn_variant, k_true=st.l_true)
         ops.gemm(attn, sa.o.weight, sa.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_GATE | ops.EPI_RES, gate=m[:, 2],
                  rows_per_batch=Lp, residual=x2d, out=x2d)
         return self._block_tail(blk, x2d, m, ctx, st, h, attn)
@@ -555,7 +561,11 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         ops.rmsnorm_rope_(qc, D, 1, ca.norm_q.weight, None, Lp, eps=self.eps)
         T = ctx.shape[0] // B
         sc = st.step_cache
-        ver = (pk["wkv"]._version, pk["bkv"]._version, ca.norm_k.weight._version)
+        # the k/v Parameters are .data views of the packed tensors with their OWN version counters: an in-place edit
+        # through the reference-named parameters (cross_attn.k.weight.copy_(), a sub-module load_state_dict, a LoRA
+        # merge) bumps those, not the packed tensor's, so all of them are part of the key
+        ver = (pk["wkv"]._version, pk["bkv"]._version, ca.norm_k.weight._version, ca.k.weight._version,
+               ca.v.weight._version, ca.k.bias._version, ca.v.bias._version)
         hit = sc["kv"].get(id(blk)) if sc is not None else None
         if hit is not None and hit[0] == ver:
             kv = hit[1]
@@ -581,9 +591,11 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
     def _geo_block(self, j, c2d, x2d, e0, ctx, st):
         """GeoAdapter block j on the control stream c (VerseCrafterWanAttentionBlock.forward :112-125)."""
         blk = self.geoada_blocks[j]
-        if j == 0:  # c = before_proj(c) + x   (x is still the embedded tokens x0 here)
+        if j == 0:  # c = before_proj(c_emb) + x   (x is still the embedded tokens x0 here)
+            # The embedded control tokens live in their own buffer (st.c_emb, the idle attention workspace): the
+            # persistent GEMM keeps loading A rows for other N tiles while finished tiles store C, so A must not alias C.
             bp = blk.before_proj
-            ops.gemm(c2d, bp.weight, bp.bias, epilogue=ops.EPI_BIAS | ops.EPI_RES, residual=x2d, out=c2d)
+            ops.gemm(st.c_emb, bp.weight, bp.bias, epilogue=ops.EPI_BIAS | ops.EPI_RES, residual=x2d, out=c2d)
         if self.record is not None:
             self.record[f"geo_in.{j}"] = c2d.view(st.B, st.Lp, -1).clone()
         m = (blk.modulation + e0).to(torch.bfloat16)
@@ -631,7 +643,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         e0 [B, 6, D], ctx [B, T, D] (embedded text).  Returns the block output WITHOUT hint/after_proj."""
         B, L, D = x.shape
         blk = getattr(self, kind)[idx]
-        st = SimpleNamespace(B=B, Lp=L, grid=tuple(grid), rope=self._rope(tuple(grid)), k_len=L, step_cache=None)
+        st = SimpleNamespace(B=B, Lp=L, grid=tuple(grid), rope=self._rope(tuple(grid)), k_len=L, l_true=L, step_cache=None)
         x2d = x.to(torch.bfloat16).reshape(B * L, D).clone()
         m = (blk.modulation + e0.to(torch.bfloat16)).to(torch.bfloat16)
         self._block(blk, x2d, m, ctx.to(torch.bfloat16).reshape(-1, D).contiguous(), st)
@@ -666,7 +678,10 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         seq_len_p = int(math.ceil(seq_len / P)) * P
         assert L <= seq_len_p, "sequence longer than seq_len"  # wan_transformer3d.py:197
         Lp = seq_len_p // P
-        st = SimpleNamespace(B=B, Lp=Lp, grid=grid, rope=self._rope(grid), k_len=L if P == 1 else Lp, step_cache=None)
+        # padded tokens (global tail) are masked as keys (k_lens=seq_lens, wan_transformer3d.py:394-399): P=1 slices the
+        # local rows to k_len, the sequence-parallel paths slice the gathered keys to l_true
+        st = SimpleNamespace(B=B, Lp=Lp, grid=grid, rope=self._rope(grid), k_len=L if P == 1 else Lp, l_true=L,
+                             step_cache=None)
         D = self.dim
 
         x2d = self._buf("x", (B * Lp, D))
@@ -682,7 +697,8 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
             should_calc = self._teacache_decide(e0, t, cond_flag)
         if should_calc:
             c2d = self._buf("c", (B * Lp, D))
-            self._patch_embed([u for u in geoada_context], self.geoada_patch_embedding, c2d, seq_len_p, Lp, "ge_a")
+            st.c_emb = self._buf("attn", (B * Lp, D))   # free until the first attention call; read by before_proj only
+            self._patch_embed([u for u in geoada_context], self.geoada_patch_embedding, st.c_emb, seq_len_p, Lp, "ge_a")
             ori = x2d.clone() if self.teacache is not None else None
             self._run_blocks(x2d, c2d, e0, ctx, st, scale)
             if self.teacache is not None:
