@@ -119,71 +119,109 @@ def _block_flops(cfg, Ls, T=512):
     return 12.0 * Ls * D * D + 4.0 * T * D * D + 4.0 * Ls * D * Fd + 4.0 * Ls * Ls * D + 4.0 * Ls * T * D
 
 
-def cpu_reference_sample(cfg_name, steps=1, warmup=0, seconds_budget=28.0):
-    """One DiT block (the reference's WanAttentionBlock.forward restated in oracle/restate.py) at the config's real
-    width and real H'xW' token grid, fp32, on all host cores.  The number of latent frames of the sample is chosen from
-    a 1-frame calibration run so that one block takes about `seconds_budget` seconds (the full 21 frames when the box
-    is fast enough); tokens/s of a whole step = sample tokens / (seconds per block * number of blocks)."""
-    from oracle import restate
+def bench_config(name, world):
+    """The `config` object of the JSON line (shared by both arms so the driver sees the same workload keys)."""
+    cfg, grid, desc = CONFIGS[name]
+    L = grid[0] * (grid[1] // 2) * (grid[2] // 2)
+    return {"workload": desc, "name": name, "tokens_per_step": 2 * L, "batch": 2, "seq_len": L,
+            "parallelism": f"ulysses_sp{world}", "l2": "working set per kernel >> 126 MB L2 (no flush needed)",
+            "teacache": "off", "cfg_skip": "off", "step_cache": "off", "weights": "random non-trivial bf16 (synthetic_init_)"}
+
+
+def cpu_reference_sample(cfg_name, steps=1, warmup=0, total_budget=150.0, max_step_seconds=28.0):
+    """CPU arm.  One "step" = one DiT block at the config's real width on a bounded sample of its token grid, fp32, on
+    all host cores — the reference's OWN `WanAttentionBlock.forward` (wan_transformer3d.py:564-611), imported unmodified
+    from /root/reference or its byte-for-byte copy under oracle/_ref (kind "reference"; attention() = torch SDPA, VideoX-Fun
+    being un-vendored), else the oracle's restatement (kind "port").  The sample = the first `frames` latent frames of the
+    real H'xW' grid, `frames` chosen from a 1-frame calibration so that one step takes about
+    min(max_step_seconds, total_budget / (steps + warmup)) seconds: exactly `warmup` + `steps` steps run within the budget.
+    Extrapolation to the metric (stated in `sample`): seconds per FULL-grid block = measured s/step x flops(full grid) /
+    flops(sample) (attention is quadratic in the token count); a denoise step = that x (num_layers + geoada blocks) x CFG
+    batch 2; tokens/s = 2 L / s_per_denoise_step.  Embeddings, adapter projections and the hint copies are left out
+    (generous to the CPU).  Returns (cpu_baseline dict, mean measured seconds per step, extrapolated s per denoise step)."""
+    from oracle import ref_import, restate
     cfg, grid, _ = CONFIGS[cfg_name]
     cores = len(os.sched_getaffinity(0))
     torch.set_num_threads(cores)
     D, H = cfg["dim"], cfg["num_heads"]
     gh, gw = grid[1] // 2, grid[2] // 2
-    shapes = restate.block_param_shapes(D, cfg["ffn_dim"])
     g = torch.Generator().manual_seed(0)
-    sd = {"b." + k: (torch.randn(s, generator=g) * (0.02 if len(s) > 1 else 0.1) + (1.0 if "norm" in k and k.endswith("weight") else 0.0))
-          for k, s in shapes.items()}
     e0 = torch.randn(1, 6, D, generator=g) * 0.1
     ctx = torch.randn(1, 512, D, generator=g)
+    if ref_import.reference_available():
+        kind = "reference"
+        base, _vc = ref_import.load_reference_modules()
+        torch.manual_seed(0)
+        blk = base.WanAttentionBlock("t2v_cross_attn", D, cfg["ffn_dim"], H, (-1, -1), True, True, 1e-6).eval().requires_grad_(False)
+        d = D // H
+        freqs = torch.cat([base.rope_params(1024, d - 4 * (d // 6)), base.rope_params(1024, 2 * (d // 6)),
+                           base.rope_params(1024, 2 * (d // 6))], dim=1)
+        src = os.path.relpath(ref_import.REF_ROOT, ROOT) if ref_import.REF_ROOT.startswith(ROOT) else ref_import.REF_ROOT
+        what = f"the reference's own WanAttentionBlock.forward ({src}, unmodified; attention() = torch SDPA)"
+
+        def block(x, sgrid):
+            return blk(x, e0, torch.tensor([x.shape[1]]), torch.tensor([list(sgrid)]), freqs, ctx, None, dtype=torch.float32)
+    else:
+        kind = "port"
+        shapes = restate.block_param_shapes(D, cfg["ffn_dim"])
+        sd = {"b." + k: (torch.randn(s, generator=g) * (0.02 if len(s) > 1 else 0.1) + (1.0 if "norm" in k and k.endswith("weight") else 0.0))
+              for k, s in shapes.items()}
+        what = "oracle/restate.dit_block (restatement of WanAttentionBlock.forward)"
+
+        def block(x, sgrid):
+            return restate.dit_block(sd, "b.", x, e0, restate.rope_angles(D // H, sgrid), ctx, H)
 
     def run_block(frames):
         sgrid = (frames, gh, gw)
-        Ls = frames * gh * gw
-        x = torch.randn(1, Ls, D, generator=g)
-        ang = restate.rope_angles(D // H, sgrid)
+        x = torch.randn(1, frames * gh * gw, D, generator=g)
         t0 = time.perf_counter()
         with torch.no_grad():
-            restate.dit_block(sd, "b.", x, e0, ang, ctx, H)
-        return time.perf_counter() - t0, Ls, sgrid
+            block(x, sgrid)
+        return time.perf_counter() - t0
 
     run_block(1)                                  # page in / thread pool
-    t_cal, L_cal, _ = run_block(1)
-    rate = _block_flops(cfg, L_cal) / t_cal       # flop/s of this box on the 1-frame block
+    t_cal = run_block(1)
+    rate = _block_flops(cfg, gh * gw) / t_cal     # flop/s of this box on the 1-frame block
+    step_budget = min(max_step_seconds, total_budget / max(1, steps + warmup))
     frames = 1
     for f in range(grid[0], 0, -1):
-        if _block_flops(cfg, f * gh * gw) / rate <= seconds_budget:
+        if _block_flops(cfg, f * gh * gw) / rate <= step_budget:
             frames = f
             break
-    times = []
-    for i in range(warmup + steps):
-        dt, Ls, sgrid = run_block(frames)
-        if i >= warmup:
-            times.append(dt)
-        if sum(times) > 2.5 * seconds_budget:
-            break
+    Ls, sgrid = frames * gh * gw, (frames, gh, gw)
+    for _ in range(warmup):
+        run_block(frames)
+    times = [run_block(frames) for _ in range(steps)]
+    t_step = sum(times) / len(times)
     n_blocks = cfg["num_layers"] + len(range(0, cfg["num_layers"], 2))
-    t_blk = sum(times) / len(times)
-    tokens_per_s = Ls / (t_blk * n_blocks)
+    B = 2
     L_full = grid[0] * gh * gw
-    return dict(value=tokens_per_s, unit="tokens/s", cores=cores, kind="port",
-                sample=f"oracle/restate.dit_block fp32 on {cores} threads: 1 block of {n_blocks} at dim {D}, 1 sample, "
-                       f"{Ls} tokens = {sgrid} of the {grid[0]}x{gh}x{gw} grid (frames chosen by a 1-frame calibration "
-                       f"for ~{seconds_budget:.0f} s/block), {len(times)} run(s), {t_blk:.2f} s/block, "
-                       f"{_block_flops(cfg, Ls) / t_blk / 1e12:.2f} TFLOP/s; tokens/s = {Ls}/(s_per_block*{n_blocks})"
-                       + ("" if Ls == L_full else f" [attention cost per token at the full L={L_full} is {L_full / Ls:.1f}x the sample's]")), t_blk
+    scale_up = _block_flops(cfg, L_full) / _block_flops(cfg, Ls)
+    s_denoise = t_step * scale_up * n_blocks * B
+    tokens_per_s = B * L_full / s_denoise
+    cb = dict(value=tokens_per_s, unit="tokens/s", cores=cores, kind=kind,
+              sample=f"{what} fp32 on {cores} threads; one step = 1 block of {n_blocks} at dim {D} on 1 sample of the CFG "
+                     f"pair, {Ls} tokens = {sgrid} of the {grid[0]}x{gh}x{gw} grid (frames from a 1-frame calibration for "
+                     f"~{step_budget:.1f} s/step); {warmup} warm-up + {len(times)} timed step(s), {t_step:.2f} s/step, "
+                     f"{_block_flops(cfg, Ls) / t_step / 1e12:.2f} TFLOP/s; full-grid block = x{scale_up:.2f} by flop count; "
+                     f"denoise step = x{n_blocks} blocks x{B} CFG = {s_denoise:.0f} s; tokens/s = {B}*{L_full}/that")
+    return cb, t_step, s_denoise
 
 
 def run_reference_arm(args):
+    """`bench.py --impl reference`: exactly --warmup + --steps bounded-sample steps on the host cores; `ms_per_step` is the
+    measured time of one such step (so steps x ms_per_step is this run's wall clock), `value` the metric extrapolated
+    from it as cpu_baseline.sample states."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cb, t_blk = cpu_reference_sample(args.config, steps=max(1, args.steps), warmup=min(args.warmup, 1))
-    cfg, grid, desc = CONFIGS[args.config]
+    cb, t_step, s_denoise = cpu_reference_sample(args.config, steps=max(1, args.steps), warmup=max(0, args.warmup))
     line = {"impl": "reference", "metric": "video_tokens_per_s", "value": cb["value"], "unit": "tokens/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_blk * 1e3,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "note": "CPU port of the reference path on a bounded sample; ms_per_step is one block of the sample"},
+            "n_gpus": args.gpus, "steps": max(1, args.steps), "warmup": max(0, args.warmup), "ms_per_step": t_step * 1e3,
+            "s_per_denoise_step": s_denoise, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": bench_config(args.config, int(os.environ.get("WORLD_SIZE", "1"))),
+            "reference_run": "host CPU; ms_per_step = one bounded-sample step (see cpu_baseline.sample), "
+                             "s_per_denoise_step / value = extrapolated whole step",
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -278,6 +316,30 @@ def run_gpu_arm(args):
     torch.cuda.synchronize()
     assert torch.isfinite(y.float()).all(), "non-finite prediction"
 
+    sp_parity = None
+    if world > 1:
+        # The sequence-parallel answer must be the single-GPU answer: every rank holds the full weights, so each one
+        # computes the P=1 forward of the same inputs locally and compares it with the gathered SP forward at the REAL
+        # shape (c3 at P=8: Lp=4095, 5 heads per rank).  Worst rank is reported; a mismatch aborts before timing.
+        y_sp = step_resident().float()
+        saved = (model.sp_world_size, model.sp_world_rank)
+        model.sp_world_size, model.sp_world_rank = 1, 0
+        y_one = step_resident().float()
+        model.sp_world_size, model.sp_world_rank = saved
+        cos = torch.nn.functional.cosine_similarity(y_sp.flatten().double(), y_one.flatten().double(), dim=0)
+        rel = (y_sp - y_one).double().norm() / y_one.double().norm()
+        stats = torch.tensor([float(cos), -float(rel), 1.0 if torch.equal(y_sp, y_one) else 0.0], device="cuda", dtype=torch.float64)
+        dist.all_reduce(stats, op=dist.ReduceOp.MIN)
+        sp_parity = {"cosine": float(stats[0]), "rel_l2": -float(stats[1]), "bit_identical": bool(stats[2] == 1.0),
+                     "mode": "fused" if model._px is not None else "nccl",
+                     "what": "gathered SP forward vs the rank-local P=1 forward of the same inputs, worst over ranks"}
+        del y_sp, y_one
+        model.release_workspace()       # the P=1 workspace is not part of the SP step
+        torch.cuda.empty_cache()
+        assert sp_parity["cosine"] >= 0.9999, f"sequence-parallel forward differs from the single-GPU forward: {sp_parity}"
+        for _ in range(2):
+            step_resident()             # re-warm after the workspace release
+
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -319,19 +381,19 @@ def run_gpu_arm(args):
     line = {"metric": "video_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "s_per_denoise_step": ms_step / 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": desc, "name": args.config, "tokens_per_step": tokens, "batch": B, "seq_len": L,
-                       "parallelism": f"ulysses_sp{world}", "l2": "working set per kernel >> 126 MB L2 (no flush needed)",
-                       "teacache": "off", "cfg_skip": "off", "step_cache": "off", "weights": "random non-trivial bf16 (synthetic_init_)"},
+            "config": bench_config(args.config, world),
             "step_pflop": (gemm_f + attn_f) / 1e15,
             "step_frac_of_bf16_sustained": (gemm_f + attn_f) / world / (ms_step * 1e9) / peaks["bf16_tflops_sustained"],
             "roofline": roofline, "kernels": kern, "clocks": clocks,
             "e2e": {"value": tokens / (ms_e2e / args.steps / 1e3), "unit": "tokens/s", "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": launches}
+    if sp_parity is not None:
+        line["sp_parity"] = sp_parity
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             try:
-                line["cpu_baseline"], _ = cpu_reference_sample(args.config, steps=1, warmup=0)
+                line["cpu_baseline"] = cpu_reference_sample(args.config, steps=1, warmup=0)[0]
             except Exception as e:  # noqa: BLE001
                 line["cpu_baseline"] = {"error": repr(e)[:200]}
         print(json.dumps(line), flush=True)

@@ -1,8 +1,11 @@
-"""TEST INFRASTRUCTURE — loads the reference's own two model files, unmodified, from /root/reference.
+"""TEST INFRASTRUCTURE — loads the reference's own two model files, unmodified.
 
-Only usable where /root/reference exists (the build container); it never runs on the GPU box.  Used by
-tests/golden/gen_golden.py to produce the committed fixtures and by the CPU tests (when the reference is
-present) to pin oracle/restate.py against the real reference code.
+Source: /root/reference where it exists (the build container), else the byte-for-byte copy that oracle/build_ref.py
+placed under the git-ignored oracle/_ref/ (it travels with the gpurun snapshot; digests pinned in
+oracle/ref_manifest.json), so the reference itself can run on the B200 under torch.autocast(bf16) with attention()
+bound to flash_attn — the "reference PyTorch + flash-attn path" north_star names.  Used by tests/golden/gen_golden.py
+to produce the committed fixtures, by the CPU tests to pin oracle/restate.py's fp32 mode, by tests/test_reference_gpu.py
+to pin its bf16 mode and the drop-in against the reference, and by bench.py's CPU arm.
 
 The import goes through oracle/ref_stub (fake `diffusers`, fake `videox_fun`) because neither package is
 installed and VideoX-Fun is an un-vendored submodule with no recoverable pin.  The only
@@ -14,12 +17,30 @@ import sys
 
 import torch
 
-REF_ROOT = os.environ.get("VC_REFERENCE_ROOT", "/root/reference")
-_STUB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_stub")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_STUB = os.path.join(_HERE, "ref_stub")
+_PROBE = "versecrafter/models/wan_transformer3d_versecrafter.py"
+
+
+def reference_root():
+    """/root/reference (or $VC_REFERENCE_ROOT) when present, else oracle/_ref if it verifies against the pinned
+    digests, else None."""
+    live = os.environ.get("VC_REFERENCE_ROOT", "/root/reference")
+    if os.path.isfile(os.path.join(live, _PROBE)):
+        return live
+    local = os.path.join(_HERE, "_ref")
+    if os.path.isfile(os.path.join(local, _PROBE)):
+        from . import build_ref
+        if build_ref.verify(local):
+            return local
+    return None
+
+
+REF_ROOT = reference_root() or "/root/reference"
 
 
 def reference_available():
-    return os.path.isfile(os.path.join(REF_ROOT, "versecrafter/models/wan_transformer3d_versecrafter.py"))
+    return os.path.isfile(os.path.join(REF_ROOT, _PROBE))
 
 
 def _load(name, path):
