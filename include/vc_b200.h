@@ -63,6 +63,24 @@ int vc_gemm_bf16(const void* A, long long lda, const void* W, long long ldw, voi
                  long long gate_batch_stride, long long rows_per_batch, const void* residual, long long ldr,
                  float scale, void* stream);
 
+/* a4 — the fp32 timestep-embedding island, wan_transformer3d_versecrafter.py:347-354:
+ *   s  = [cos(t w_j) | sin(t w_j)], w_j = 10000^(-j/(freq_dim/2))  in fp64, rounded to fp32   (wan_transformer3d.py:39-49)
+ *   e  = W2 silu(W0 s + b0) + b2                                    (time_embedding, :764-765)
+ *   e0 = Wp silu(e) + bp                                            (time_projection, :766), viewed [B, 6, D]
+ * fp32 arithmetic on the bf16-valued weights (w0 [D, freq_dim], w2 [D, D], wp [6D, D], row-major, contiguous), outputs
+ * rounded once to bf16: e_out [B, D], e0_out [B, 6D].  t: fp64 [B] on the device (1 <= B <= 8).
+ * workspace: caller-provided fp32 scratch of at least B * (freq_dim + 2 D) elements, 16-byte aligned. */
+int vc_time_embed(const double* t, int B, int freq_dim, int D, const void* w0, const void* b0, const void* w2,
+                  const void* b2, const void* wp, const void* bp, void* e_out, void* e0_out, float* workspace,
+                  void* stream);
+
+/* a4/a6 — `self.modulation + e` of every block in one launch (wan_transformer3d.py:588 per block, Head :640-643):
+ *   out[i, b, :]  = bf16(block_modulations[i][0:6D] + e0[b, 0:6D])      i < n_blocks   (out: [n_blocks, B, 6D])
+ *   out_head[b,:] = bf16(head_modulation[0:2D] + (e[b] | e[b]))          when head_modulation != NULL  ([B, 2D])
+ * block_modulations: DEVICE array of n_blocks device pointers to the blocks' [1, 6, D] parameters. */
+int vc_modulation_table(const void* const* block_modulations, int n_blocks, const void* e0, int B, int D, void* out,
+                        const void* head_modulation, const void* e, void* out_head, void* stream);
+
 /* K6/K7 — o = softmax(q k^T * softmax_scale) v, non-causal, all Lk keys attended (no mask other than the tail of
  * the last 128-key tile).  Replaces videox_fun attention() at wan_transformer3d.py:394-399 (self) and :425-430
  * (cross).  head_dim must be 128 and contiguous; *_strides = {batch, token, head} strides in elements (so q/k/v

@@ -360,3 +360,39 @@ def test_errors_are_reported(ops):
         ops.gemm(a, w, None)  # K % 8 != 0
     with pytest.raises(_lib.VCError):
         ops.gemm(a.cpu(), w.cpu(), None)  # no CPU fallback
+
+
+@pytest.mark.parametrize("B,D,freq_dim,tvals", [(2, 512, 256, (500.0, 500.0)), (2, 1536, 256, (999.0, 3.0)),
+                                                 (1, 5120, 256, (731.0,)), (3, 256, 64, (0.0, 17.5, 1000.0))])
+def test_time_embed_island(ops, B, D, freq_dim, tvals):
+    """a4: fp64 sinusoid -> time_embedding -> time_projection, fp32 on bf16-valued weights, vs the oracle (pinned to the
+    reference's fp32 island).  Only the fp32 summation order differs from cuBLAS: outputs agree to the last bf16 bit
+    almost everywhere."""
+    sd = {"time_embedding.0.weight": _rand((D, freq_dim), 60, 0.02), "time_embedding.0.bias": _rand((D,), 61, 0.02),
+          "time_embedding.2.weight": _rand((D, D), 62, 0.02), "time_embedding.2.bias": _rand((D,), 63, 0.02),
+          "time_projection.1.weight": _rand((6 * D, D), 64, 1 / math.sqrt(D)), "time_projection.1.bias": _rand((6 * D,), 65, 0.02)}
+    t = torch.tensor(tvals, device="cuda")
+    e_ref, e0_ref = restate.time_embed(sd, t, freq_dim, D, torch.bfloat16)
+    for tt in (t, t.double(), t.long() if all(float(v).is_integer() for v in tvals) else t):
+        e, e0 = ops.time_embed(tt, sd["time_embedding.0.weight"], sd["time_embedding.0.bias"], sd["time_embedding.2.weight"],
+                               sd["time_embedding.2.bias"], sd["time_projection.1.weight"], sd["time_projection.1.bias"])
+        assert e.shape == (B, D) and e0.shape == (B, 6, D)
+        assert relerr(e, e_ref) < 2e-3 and relerr(e0, e0_ref) < 2e-3
+        assert float((e0 != e0_ref).float().mean()) < 0.02 and float((e != e_ref).float().mean()) < 0.02
+
+
+def test_modulation_table_is_the_bf16_add(ops):
+    """m[i, b] = modulation_i + e0[b] for all blocks in one launch: bit-identical to torch's bf16 add."""
+    B, D, n = 2, 640, 5
+    mods = [_rand((1, 6, D), 70 + i, 0.05) for i in range(n)]
+    e0, e, head = _rand((B, 6, D), 80, 0.3), _rand((B, D), 81, 0.3), _rand((1, 2, D), 82, 0.05)
+    ptrs = torch.tensor([m.data_ptr() for m in mods], dtype=torch.int64).cuda()
+    out = torch.empty((n, B, 6, D), device="cuda", dtype=torch.bfloat16)
+    out_head = torch.empty((B, 2, D), device="cuda", dtype=torch.bfloat16)
+    ops.modulation_table(ptrs, n, e0, out, head, e, out_head)
+    for i in range(n):
+        assert torch.equal(out[i], mods[i] + e0)
+    assert torch.equal(out_head, head + e[:, None, :])
+    out2 = torch.zeros_like(out)
+    ops.modulation_table(ptrs, n, e0, out2)          # without the head table
+    assert torch.equal(out2, out)

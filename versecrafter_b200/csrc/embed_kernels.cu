@@ -1,0 +1,200 @@
+// Timestep-embedding island and the per-block modulation table.
+//
+// Replaces, per denoise step, the fp32 autocast island of the reference
+//   sinusoidal_embedding_1d -> time_embedding (Linear, SiLU, Linear) -> time_projection (SiLU, Linear)
+//   (wan_transformer3d.py:39-49, :764-766; wan_transformer3d_versecrafter.py:347-354)
+// and the `self.modulation + e` of every block and of the head (wan_transformer3d.py:588, :640-643):
+//   vc_time_embed       : t[B] -> e[B,D] (bf16), e0[B,6D] (bf16); fp64 sinusoid, fp32 MLP with the bf16-valued weights
+//   vc_modulation_table : m[i,b,:] = bf16(modulation_i + e0[b]) for all blocks in ONE launch (+ the head's 2-chunk table)
+// The matmuls have M = B (1..8 rows): they are weight-streaming GEMVs (370 MB of weights at D = 5120), HBM-bound, so the
+// kernel is a warp-per-output-row reduction with 16-byte coalesced weight loads — not a tensor-core GEMM.
+// Compiled WITHOUT --use_fast_math (build.py PRECISE_SOURCES): SiLU uses IEEE division and expf, as torch does.
+#include "common.cuh"
+
+namespace {
+
+constexpr int MAX_B = 8;
+constexpr int GEMV_THREADS = 256;   // 8 warps
+constexpr int ROWS_PER_WARP = 2;
+
+__global__ void sinusoid_kernel(const double* __restrict__ t, int B, int half, float* __restrict__ s) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * half) return;
+  const int b = i / half, j = i - b * half;
+  // [cos(t w_j) | sin(t w_j)], w_j = 10000^(-j/half), evaluated in fp64 and rounded to fp32 (:39-49)
+  const double ang = t[b] * pow(10000.0, -static_cast<double>(j) / static_cast<double>(half));
+  s[(long long)b * 2 * half + j] = static_cast<float>(cos(ang));
+  s[(long long)b * 2 * half + half + j] = static_cast<float>(sin(ang));
+}
+
+__device__ __forceinline__ float silu(float x) { return x / (1.0f + expf(-x)); }
+
+// out[b, n] = sum_k W[n, k] * in[b, k] + bias[n]       (W bf16 [N, K] row stride ldw, in fp32 [B, K], fp32 accumulate)
+// act: bit 0 -> out_raw (fp32), bit 1 -> out_silu = silu(.) (fp32), bit 2 -> out_bf16 (bf16 of the raw value)
+template <int kB>
+__global__ void __launch_bounds__(GEMV_THREADS)
+gemv_bf16w_kernel(const __nv_bfloat16* __restrict__ W, long long ldw, const __nv_bfloat16* __restrict__ bias,
+                  const float* __restrict__ in, int K, int N, float* __restrict__ out_raw, float* __restrict__ out_silu,
+                  __nv_bfloat16* __restrict__ out_bf16, int act) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row0 = (blockIdx.x * (GEMV_THREADS / 32) + warp) * ROWS_PER_WARP;
+  if (row0 >= N) return;
+  float acc[ROWS_PER_WARP][kB];
+#pragma unroll
+  for (int r = 0; r < ROWS_PER_WARP; ++r)
+#pragma unroll
+    for (int b = 0; b < kB; ++b) acc[r][b] = 0.f;
+  const int chunks = K >> 3;  // 8 bf16 = 16 bytes
+  for (int c = lane; c < chunks; c += 32) {
+    float x[kB][8];
+#pragma unroll
+    for (int b = 0; b < kB; ++b) {
+      const float4 lo = __ldg(reinterpret_cast<const float4*>(in + (long long)b * K + c * 8));
+      const float4 hi = __ldg(reinterpret_cast<const float4*>(in + (long long)b * K + c * 8 + 4));
+      x[b][0] = lo.x; x[b][1] = lo.y; x[b][2] = lo.z; x[b][3] = lo.w;
+      x[b][4] = hi.x; x[b][5] = hi.y; x[b][6] = hi.z; x[b][7] = hi.w;
+    }
+#pragma unroll
+    for (int r = 0; r < ROWS_PER_WARP; ++r) {
+      const int row = min(row0 + r, N - 1);
+      const uint4 wu = __ldg(reinterpret_cast<const uint4*>(W + (long long)row * ldw + c * 8));
+      const float2 w0 = vc::unpack_bf16x2(wu.x), w1 = vc::unpack_bf16x2(wu.y), w2 = vc::unpack_bf16x2(wu.z),
+                   w3 = vc::unpack_bf16x2(wu.w);
+#pragma unroll
+      for (int b = 0; b < kB; ++b) {
+        float a = acc[r][b];
+        a = fmaf(w0.x, x[b][0], a); a = fmaf(w0.y, x[b][1], a); a = fmaf(w1.x, x[b][2], a); a = fmaf(w1.y, x[b][3], a);
+        a = fmaf(w2.x, x[b][4], a); a = fmaf(w2.y, x[b][5], a); a = fmaf(w3.x, x[b][6], a); a = fmaf(w3.y, x[b][7], a);
+        acc[r][b] = a;
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < ROWS_PER_WARP; ++r)
+#pragma unroll
+    for (int b = 0; b < kB; ++b) {
+      float a = acc[r][b];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+      acc[r][b] = a;
+    }
+  if (lane == 0) {
+#pragma unroll
+    for (int r = 0; r < ROWS_PER_WARP; ++r) {
+      const int row = row0 + r;
+      if (row < N) {
+        const float bv = bias ? __bfloat162float(bias[row]) : 0.f;
+#pragma unroll
+        for (int b = 0; b < kB; ++b) {
+          const float v = acc[r][b] + bv;
+          if (act & 1) out_raw[(long long)b * N + row] = v;
+          if (act & 2) out_silu[(long long)b * N + row] = silu(v);
+          if (act & 4) out_bf16[(long long)b * N + row] = __float2bfloat16_rn(v);
+        }
+      }
+    }
+  }
+}
+
+template <int kB>
+void launch_gemv(const void* W, long long ldw, const void* bias, const float* in, int K, int N, float* out_raw,
+                 float* out_silu, void* out_bf16, int act, cudaStream_t s) {
+  const int rows_per_cta = (GEMV_THREADS / 32) * ROWS_PER_WARP;
+  gemv_bf16w_kernel<kB><<<(N + rows_per_cta - 1) / rows_per_cta, GEMV_THREADS, 0, s>>>(
+      (const __nv_bfloat16*)W, ldw, (const __nv_bfloat16*)bias, in, K, N, out_raw, out_silu, (__nv_bfloat16*)out_bf16, act);
+}
+
+void gemv(int B, const void* W, long long ldw, const void* bias, const float* in, int K, int N, float* out_raw,
+          float* out_silu, void* out_bf16, int act, cudaStream_t s) {
+  // batch rows in groups of <= 4 (register budget); B is the CFG batch (1 or 2) in every caller
+  for (int b0 = 0; b0 < B; b0 += 4) {
+    const int nb = B - b0 < 4 ? B - b0 : 4;
+    const float* in_b = in + (long long)b0 * K;
+    float* raw_b = out_raw ? out_raw + (long long)b0 * N : nullptr;
+    float* silu_b = out_silu ? out_silu + (long long)b0 * N : nullptr;
+    void* bf_b = out_bf16 ? (void*)((__nv_bfloat16*)out_bf16 + (long long)b0 * N) : nullptr;
+    switch (nb) {
+      case 1: launch_gemv<1>(W, ldw, bias, in_b, K, N, raw_b, silu_b, bf_b, act, s); break;
+      case 2: launch_gemv<2>(W, ldw, bias, in_b, K, N, raw_b, silu_b, bf_b, act, s); break;
+      case 3: launch_gemv<3>(W, ldw, bias, in_b, K, N, raw_b, silu_b, bf_b, act, s); break;
+      default: launch_gemv<4>(W, ldw, bias, in_b, K, N, raw_b, silu_b, bf_b, act, s); break;
+    }
+  }
+}
+
+// m[i, b, :] = bf16(float(mod_i[:]) + float(e0[b, :]))  for i < n_blocks (6D-wide rows), and the head's
+// mh[b, :] = bf16(float(head_mod[:]) + float(e[b, c % D]))  (2D-wide rows; e broadcast over the 2 chunks).
+// A bf16 + bf16 torch add is exactly this: fp32 sum of the two bf16 values, rounded once.
+__global__ void modulation_table_kernel(const __nv_bfloat16* const* __restrict__ mods, int n_blocks,
+                                        const __nv_bfloat16* __restrict__ e0, int B, int D,
+                                        __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ head_mod,
+                                        const __nv_bfloat16* __restrict__ e, __nv_bfloat16* __restrict__ out_head) {
+  const long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // one 8-element (16-byte) vector per thread
+  const long long row_vecs = 6LL * D / 8;
+  const long long n_main = (long long)n_blocks * B * row_vecs;
+  const __nv_bfloat16 *pa, *pb;
+  __nv_bfloat16* po;
+  if (v < n_main) {
+    const long long i = v / (B * row_vecs);
+    const long long rem = v - i * (B * row_vecs);
+    const long long b = rem / row_vecs, c = (rem - b * row_vecs) * 8;
+    pa = mods[i] + c;
+    pb = e0 + b * 6LL * D + c;
+    po = out + (i * B + b) * 6LL * D + c;
+  } else {
+    const long long h = v - n_main;
+    const long long head_vecs = 2LL * D / 8;
+    if (!head_mod || h >= (long long)B * head_vecs) return;
+    const long long b = h / head_vecs, c = (h - b * head_vecs) * 8;
+    pa = head_mod + c;
+    pb = e + b * (long long)D + (c % D);
+    po = out_head + b * 2LL * D + c;
+  }
+  const uint4 ua = __ldg(reinterpret_cast<const uint4*>(pa));
+  const uint4 ub = __ldg(reinterpret_cast<const uint4*>(pb));
+  const uint32_t a4[4] = {ua.x, ua.y, ua.z, ua.w}, b4[4] = {ub.x, ub.y, ub.z, ub.w};
+  uint32_t o4[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 fa = vc::unpack_bf16x2(a4[j]), fb = vc::unpack_bf16x2(b4[j]);
+    o4[j] = vc::pack_bf16x2(fa.x + fb.x, fa.y + fb.y);
+  }
+  *reinterpret_cast<uint4*>(po) = make_uint4(o4[0], o4[1], o4[2], o4[3]);
+}
+
+}  // namespace
+
+extern "C" int vc_time_embed(const double* t, int B, int freq_dim, int D, const void* w0, const void* b0, const void* w2,
+                             const void* b2, const void* wp, const void* bp, void* e_out, void* e0_out, float* workspace,
+                             void* stream) {
+  VC_CHECK_ARG(t && w0 && b0 && w2 && b2 && wp && bp && e_out && e0_out && workspace, "vc_time_embed: null pointer");
+  VC_CHECK_ARG(B >= 1 && B <= MAX_B, "vc_time_embed: batch %d outside 1..%d", B, MAX_B);
+  VC_CHECK_ARG(freq_dim > 0 && freq_dim % 16 == 0 && D > 0 && D % 8 == 0,
+               "vc_time_embed: freq_dim must be a multiple of 16 and D a multiple of 8 (freq_dim=%d D=%d)", freq_dim, D);
+  VC_CHECK_ARG(((uintptr_t)w0 | (uintptr_t)w2 | (uintptr_t)wp | (uintptr_t)workspace) % 16 == 0,
+               "vc_time_embed: weights and workspace must be 16-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  // workspace (fp32): sinusoid [B, freq_dim] | h1 = silu(W0 s + b0) [B, D] | silu(e) [B, D]
+  float* sinus = workspace;
+  float* h1 = sinus + (long long)B * freq_dim;
+  float* e_silu = h1 + (long long)B * D;
+  const int half = freq_dim / 2;
+  sinusoid_kernel<<<(B * half + 127) / 128, 128, 0, s>>>(t, B, half, sinus);
+  gemv(B, w0, freq_dim, b0, sinus, freq_dim, D, nullptr, h1, nullptr, 2, s);         // time_embedding.0 + SiLU
+  gemv(B, w2, D, b2, h1, D, D, nullptr, e_silu, e_out, 2 | 4, s);                     // time_embedding.2 -> e; SiLU(e)
+  gemv(B, wp, D, bp, e_silu, D, 6 * D, nullptr, nullptr, e0_out, 4, s);               // time_projection.1 -> e0
+  VC_RETURN_LAUNCH_STATUS("vc_time_embed");
+}
+
+extern "C" int vc_modulation_table(const void* const* block_modulations, int n_blocks, const void* e0, int B, int D,
+                                   void* out, const void* head_modulation, const void* e, void* out_head, void* stream) {
+  VC_CHECK_ARG(n_blocks >= 0 && B >= 1 && D > 0 && D % 8 == 0, "vc_modulation_table: bad sizes n=%d B=%d D=%d", n_blocks, B, D);
+  VC_CHECK_ARG(n_blocks == 0 || (block_modulations && e0 && out), "vc_modulation_table: null pointer");
+  VC_CHECK_ARG(!head_modulation || (e && out_head), "vc_modulation_table: head table without e / out_head");
+  const long long vecs = (long long)n_blocks * B * 6 * D / 8 + (head_modulation ? (long long)B * 2 * D / 8 : 0);
+  if (vecs == 0) return 0;
+  modulation_table_kernel<<<(unsigned)((vecs + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16* const*)block_modulations, n_blocks, (const __nv_bfloat16*)e0, B, D, (__nv_bfloat16*)out,
+      (const __nv_bfloat16*)head_modulation, (const __nv_bfloat16*)e, (__nv_bfloat16*)out_head);
+  VC_RETURN_LAUNCH_STATUS("vc_modulation_table");
+}

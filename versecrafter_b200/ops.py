@@ -144,6 +144,52 @@ def rmsnorm_rope_(buf, D, n_mats, gain_q, gain_k, rows_per_batch, eps=1e-6, rope
     return buf
 
 
+def time_embed(t, w0, b0, w2, b2, wp, bp, e_out=None, e0_out=None, workspace=None):
+    """fp32 timestep-embedding island: t [B] (any real dtype) -> (e [B, D] bf16, e0 [B, 6, D] bf16).  Four launches
+    (fp64 sinusoid + three weight-streaming GEMVs); w0 [D, freq_dim], w2 [D, D], wp [6D, D] bf16."""
+    global launch_count
+    for u, n in ((w0, "w0"), (b0, "b0"), (w2, "w2"), (b2, "b2"), (wp, "wp"), (bp, "bp")):
+        _chk(u, n)
+        if not u.is_contiguous():
+            raise _lib.VCError(f"time_embed: {n} must be contiguous")
+    if not t.is_cuda:
+        raise _lib.VCError("time_embed: t must be a CUDA tensor")
+    B, (D, freq_dim) = t.numel(), w0.shape
+    t64 = t.reshape(-1).to(torch.float64)
+    dev = w0.device
+    if e_out is None:
+        e_out = torch.empty((B, D), dtype=torch.bfloat16, device=dev)
+    if e0_out is None:
+        e0_out = torch.empty((B, 6, D), dtype=torch.bfloat16, device=dev)
+    if workspace is None:
+        workspace = torch.empty(B * (freq_dim + 2 * D), dtype=torch.float32, device=dev)
+    assert workspace.dtype == torch.float32 and workspace.numel() >= B * (freq_dim + 2 * D)
+    lib = _lib.load()
+    with _timed("time_embed", 2.0 * (D * freq_dim + 7 * D * D)):
+        _lib.check(lib.vc_time_embed(_ptr(t64), B, freq_dim, D, _ptr(w0), _ptr(b0), _ptr(w2), _ptr(b2), _ptr(wp), _ptr(bp),
+                                     _ptr(e_out), _ptr(e0_out), _ptr(workspace), _stream()), "vc_time_embed")
+    launch_count += 4
+    return e_out, e0_out
+
+
+def modulation_table(mod_ptrs, n_blocks, e0, out, head_mod=None, e=None, out_head=None):
+    """out[i, b] = bf16(modulation_i + e0[b]) for every block in one launch; mod_ptrs: int64 CUDA tensor holding the
+    device addresses of the blocks' [1, 6, D] modulation parameters.  Optionally the head's [B, 2, D] table from e."""
+    global launch_count
+    _chk(e0, "e0"); _chk(out, "out")
+    B, D = e0.shape[0], e0.shape[-1]
+    assert e0.is_contiguous() and out.is_contiguous() and out.numel() >= n_blocks * B * 6 * D
+    assert mod_ptrs.dtype == torch.int64 and mod_ptrs.is_cuda and mod_ptrs.numel() >= n_blocks
+    if head_mod is not None:
+        _chk(head_mod, "head_mod"); _chk(e, "e"); _chk(out_head, "out_head")
+        assert e.is_contiguous() and out_head.is_contiguous() and head_mod.is_contiguous()
+    lib = _lib.load()
+    _lib.check(lib.vc_modulation_table(_ptr(mod_ptrs), n_blocks, _ptr(e0), B, D, _ptr(out), _ptr(head_mod), _ptr(e),
+                                       _ptr(out_head), _stream()), "vc_modulation_table")
+    launch_count += 1
+    return out
+
+
 def gemm(a, w, bias=None, epilogue=None, gate=None, rows_per_batch=0, residual=None, scale=1.0, out=None):
     """out[M,N] = epilogue(a[M,K] @ w[N,K]^T).  a / out / residual may be row-strided 2-D views."""
     global launch_count

@@ -215,6 +215,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         self.implicit_patch_embed = os.environ.get("VC_PATCH_EMBED", "implicit") != "explicit"
         self._ws = {}
         self._rope_cache = {}
+        self._mod_ptr_cache = {}
         # step-invariant results kept across denoising steps: embedded text and every block's
         # normalised cross-attention K|V depend only on the prompt embeddings and the weights, yet the reference
         # recomputes them in all 60 blocks of all 50 steps (wan_transformer3d.py:420-424).  Private storage (not the
@@ -452,19 +453,33 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         return r
 
     def _time_embed(self, t):
-        """fp32 island (wan_transformer3d_versecrafter.py:347-354).  2 x freq_dim inputs: host-side torch math on a
-        [B, D] problem, not a kernel of the hot path."""
-        half = self.freq_dim // 2
-        pos = t.to(torch.float64)
-        w = torch.pow(torch.tensor(10000.0, dtype=torch.float64, device=t.device),
-                      -torch.arange(half, dtype=torch.float64, device=t.device) / half)
-        ang = pos[:, None] * w[None]
-        s = torch.cat([ang.cos(), ang.sin()], dim=1).float()
+        """fp32 island (wan_transformer3d_versecrafter.py:347-354): fp64 sinusoid + time_embedding + time_projection as
+        four launches of vc_time_embed (weight-streaming GEMVs, M = CFG batch).  -> (e [B, D], e0 [B, 6, D]) bf16."""
+        B = t.numel()
         te0, te2, tp = self.time_embedding[0], self.time_embedding[2], self.time_projection[1]
-        F = torch.nn.functional
-        e = F.linear(F.silu(F.linear(s, te0.weight.float(), te0.bias.float())), te2.weight.float(), te2.bias.float())
-        e0 = F.linear(F.silu(e), tp.weight.float(), tp.bias.float()).unflatten(1, (6, self.dim))
-        return e.to(torch.bfloat16), e0.to(torch.bfloat16)
+        return ops.time_embed(t, te0.weight, te0.bias, te2.weight, te2.bias, tp.weight, tp.bias,
+                              e_out=self._buf("te_e", (B, self.dim)), e0_out=self._buf("te_e0", (B, 6, self.dim)),
+                              workspace=self._buf("te_ws", (B * (self.freq_dim + 2 * self.dim),), torch.float32))
+
+    def _modulation_tables(self, e, e0):
+        """`self.modulation + e` of all blocks and of the head (wan_transformer3d.py:588, :640-643) in ONE launch:
+        -> (m_all [num_layers + n_geo, B, 6, D], mh [B, 2, D]); backbone layer i is row i, GeoAdapter block j row
+        num_layers + j."""
+        blks = list(self.blocks) + list(self.geoada_blocks)
+        B = e0.shape[0]
+        m_all = self._buf("m_all", (len(blks), B, 6, self.dim))
+        mh = self._buf("m_head", (B, 2, self.dim))
+        ops.modulation_table(self._mod_ptrs(blks), len(blks), e0, m_all, self.head.modulation, e, mh)
+        return m_all, mh
+
+    def _mod_ptrs(self, blks):
+        """int64 device tensor with the addresses of the blocks' modulation parameters (rebuilt when one moves)."""
+        addrs = tuple(b.modulation.data_ptr() for b in blks)
+        ent = self._mod_ptr_cache.get(len(blks))
+        if ent is None or ent[0] != addrs or ent[1].device != self.device:
+            ent = (addrs, torch.tensor(addrs, dtype=torch.int64).to(self.device))
+            self._mod_ptr_cache[len(blks)] = ent
+        return ent[1]
 
     def _text_embed(self, context):
         """-> (ctx [B*text_len, D], cache dict or None).  With the step cache on, a repeated call with the same prompt
@@ -598,8 +613,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
             ops.gemm(st.c_emb, bp.weight, bp.bias, epilogue=ops.EPI_BIAS | ops.EPI_RES, residual=x2d, out=c2d)
         if self.record is not None:
             self.record[f"geo_in.{j}"] = c2d.view(st.B, st.Lp, -1).clone()
-        m = (blk.modulation + e0).to(torch.bfloat16)
-        self._block(blk, c2d, m, ctx, st)
+        self._block(blk, c2d, st.m_all[self.num_layers + j], ctx, st)
         if self.record is not None:
             self.record[f"geo_out.{j}"] = c2d.view(st.B, st.Lp, -1).clone()
 
@@ -619,8 +633,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
                     next_geo += 1
             if self.record is not None:
                 self.record[f"blk_in.{i}"] = x2d.view(st.B, st.Lp, -1).clone()
-            m = (blk.modulation + e0).to(torch.bfloat16)
-            self._block(blk, x2d, m, ctx, st)
+            self._block(blk, x2d, st.m_all[i], ctx, st)
             if j is not None:
                 if j in stored:
                     hint = stored.pop(j)
@@ -645,7 +658,10 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         blk = getattr(self, kind)[idx]
         st = SimpleNamespace(B=B, Lp=L, grid=tuple(grid), rope=self._rope(tuple(grid)), k_len=L, l_true=L, step_cache=None)
         x2d = x.to(torch.bfloat16).reshape(B * L, D).clone()
-        m = (blk.modulation + e0.to(torch.bfloat16)).to(torch.bfloat16)
+        m = torch.empty((1, B, 6, D), dtype=torch.bfloat16, device=self.device)
+        ptr = torch.tensor([blk.modulation.data_ptr()], dtype=torch.int64).to(self.device)
+        ops.modulation_table(ptr, 1, e0.to(torch.bfloat16).contiguous(), m)
+        m = m[0]
         self._block(blk, x2d, m, ctx.to(torch.bfloat16).reshape(-1, D).contiguous(), st)
         return x2d.view(B, L, D)
 
@@ -684,13 +700,16 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
                              step_cache=None)
         D = self.dim
 
-        x2d = self._buf("x", (B * Lp, D))
-        self._patch_embed(samples, self.patch_embedding, x2d, seq_len_p, Lp, "pe_a")
+        # embeddings of t and the text first (their host-side staging copies are the only torch ops of the step), so that
+        # from the first patch-embedding launch to the unpatchify every launch is a kernel of this library
         t = t.to(self.device)
         e, e0 = self._time_embed(t)
+        st.m_all, mh = self._modulation_tables(e, e0)
         ctx, st.step_cache = self._text_embed(context)
+        x2d = self._buf("x", (B * Lp, D))
+        self._patch_embed(samples, self.patch_embedding, x2d, seq_len_p, Lp, "pe_a")
         if self.record is not None:
-            self.record.update(x0=x2d.view(B, Lp, D).clone(), e=e, e0=e0, ctx=ctx.view(B, -1, D).clone())
+            self.record.update(x0=x2d.view(B, Lp, D).clone(), e=e.clone(), e0=e0.clone(), ctx=ctx.view(B, -1, D).clone())
 
         should_calc = True
         if self.teacache is not None:
@@ -713,7 +732,6 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
             x2d.add_(prev.to(x2d.device)[-x2d.shape[0]:])
 
         # head (wan_transformer3d.py:631-644)
-        mh = (self.head.modulation + e[:, None, :]).to(torch.bfloat16)
         hh = ops.ln_modulate(x2d, mh[:, 0], mh[:, 1], Lp, eps=self.eps, out=self._buf("h", (B * Lp, D)))
         yv = ops.gemm(hh, self.head.head.weight, self.head.head.bias).view(B, Lp, -1)
         if self.record is not None:
@@ -740,6 +758,6 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
             calc = not (tc.accumulated_rel_l1_distance < tc.rel_l1_thresh)
             if calc:
                 tc.accumulated_rel_l1_distance = 0
-        tc.previous_modulated_input = inp
+        tc.previous_modulated_input = inp.clone()  # e0 lives in a workspace buffer that the next step overwrites
         tc.should_calc = calc
         return calc
