@@ -58,6 +58,10 @@ int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_p
 #define VC_EPI_SCALE 16
 /* schedule bit, not arithmetic: run as clusters of two CTAs that share the W tile by TMA multicast (same results) */
 #define VC_GEMM_SCHED_MULTICAST 64
+/* CTA pair: one tcgen05.mma.cta_group::2 of M = 256 per pair of CTAs (each holds its 128 A rows and half of the W tile) */
+#define VC_GEMM_SCHED_PAIR 128
+/* one CTA per 128 x 256 tile, whatever VC_GEMM_SCHED says */
+#define VC_GEMM_SCHED_SINGLE 256
 int vc_gemm_bf16(const void* A, long long lda, const void* W, long long ldw, void* C, long long ldc, long long M,
                  long long N, long long K, int epilogue, const void* bias, const void* gate,
                  long long gate_batch_stride, long long rows_per_batch, const void* residual, long long ldr,

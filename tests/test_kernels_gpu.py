@@ -174,10 +174,33 @@ def test_gemm_multicast_schedule_is_bit_identical(ops, M, N, K, epi):
     a, w, b = _rand((M, K), 31), _rand((N, K), 32, 1 / math.sqrt(K)), _rand((N,), 33, 0.1)
     gate, res = _rand((2, N), 34, 0.5), _rand((M, N), 35)
     kw = dict(gate=gate if epi & 4 else None, rows_per_batch=(M + 1) // 2, residual=res if epi & 8 else None)
-    plain = ops.gemm(a, w, b, epilogue=epi, **kw)
+    plain = ops.gemm(a, w, b, epilogue=epi | ops.SCHED_SINGLE, **kw)
     mc = ops.gemm(a, w, b, epilogue=epi | ops.SCHED_MULTICAST, **kw)
     assert torch.equal(plain, mc)
     assert relerr(mc, _gemm_ref(a, w, b, epi, gate, (M + 1) // 2, res, 1.0)) < 4e-3
+
+
+@pytest.mark.parametrize("M,N,K", [(650, 768, 512), (129, 256, 64), (1950, 1536, 2048), (4096, 5120, 512), (256, 64, 128),
+                                   (8190, 1536, 1536), (300, 520, 72)])
+@pytest.mark.parametrize("epi", [0, 1, 3, 9, 13, 25])
+def test_gemm_cta_pair_schedule_is_bit_identical(ops, M, N, K, epi):
+    """cta_group::2: one tcgen05.mma of M = 256 per CTA pair, each CTA holding its 128 A rows and half of the W tile (odd
+    and even M-tile counts, N and K tails, every epilogue) — same bits as the one-CTA-per-tile kernel."""
+    a, w, b = _rand((M, K), 36), _rand((N, K), 37, 1 / math.sqrt(K)), _rand((N,), 38, 0.1)
+    gate, res = _rand((2, N), 39, 0.5), _rand((M, N), 40)
+    kw = dict(gate=gate if epi & 4 else None, rows_per_batch=(M + 1) // 2, residual=res if epi & 8 else None, scale=0.6)
+    bias = b if epi & 1 else None
+    plain = ops.gemm(a, w, bias, epilogue=epi | ops.SCHED_SINGLE, **kw)
+    pair = ops.gemm(a, w, bias, epilogue=epi | ops.SCHED_PAIR, **kw)
+    assert torch.equal(plain, pair)
+    assert relerr(pair, _gemm_ref(a, w, bias, epi, gate, (M + 1) // 2, res, 0.6)) < 4e-3
+
+
+def test_gemm_cta_pair_many_waves(ops):
+    """Persistent pair schedule over many waves with both accumulator stages and all six smem stages cycling."""
+    M, N, K = 148 * 128 * 2 + 77, 1024, 1024
+    a, w, b = _rand((M, K), 41), _rand((N, K), 42, 1 / math.sqrt(K)), _rand((N,), 43, 0.1)
+    assert torch.equal(ops.gemm(a, w, b, epilogue=1 | ops.SCHED_SINGLE), ops.gemm(a, w, b, epilogue=1 | ops.SCHED_PAIR))
 
 
 def test_gemm_inplace_residual_and_strided_views(ops):
@@ -255,7 +278,7 @@ def test_flash_attn_large_scores_rescale(ops):
 
 @pytest.mark.parametrize("P,H,grid", [(2, 16, (2, 8, 24)), (4, 16, (2, 8, 24)), (8, 16, (2, 8, 24)),
                                       (8, 40, (3, 13, 40)),    # c3's head split (5 heads per rank), Lp = 195: ragged
-                                      (4, 40, (5, 6, 13))])    # Q tiles and a token scatter that splits inside a tile
+                                      (4, 40, (5, 6, 12))])    # Q tiles and a token scatter that splits inside a tile
 def test_ulysses_fused_kernels_emulated_ranks(ops, P, H, grid):
     """The fused Ulysses kernels with the P ranks emulated on ONE GPU (the "peer" buffers are P local tensors): the
     head-scatter inside RMSNorm+RoPE and the token-scatter inside the attention epilogue must reproduce, bit for bit,

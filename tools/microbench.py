@@ -89,6 +89,39 @@ def bench_gemm(M, N, K, epi="bias"):
               cublas_ms=ref_avg, cublas_tflops=flops / ref_avg / 1e9, rel_err_vs_cublas=err))
 
 
+def bench_gemm_sched(M, N, K, epi="bias", rounds=4, iters=4):
+    """The three schedules of vc_gemm_bf16 (one CTA per tile / multicast cluster / cta_group::2 pair) and cuBLASLt on one
+    shape, interleaved round-robin so they see the same thermal / power state."""
+    a = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16) / math.sqrt(K)
+    b = torch.randn(N, device="cuda", dtype=torch.bfloat16)
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    base, kw = 1, {}
+    if epi == "gelu":
+        base = 3
+    elif epi == "gate_res":
+        gate = torch.randn(2, N, device="cuda", dtype=torch.bfloat16)
+        res = torch.randn(M, N, device="cuda", dtype=torch.bfloat16)
+        base, kw = 13, dict(gate=gate, rows_per_batch=(M + 1) // 2, residual=res)
+    arms = {"single": lambda: ops.gemm(a, w, b, out=out, epilogue=base | ops.SCHED_SINGLE, **kw),
+            "mc": lambda: ops.gemm(a, w, b, out=out, epilogue=base | ops.SCHED_MULTICAST, **kw),
+            "pair": lambda: ops.gemm(a, w, b, out=out, epilogue=base | ops.SCHED_PAIR, **kw),
+            "cublaslt": lambda: torch.nn.functional.linear(a, w, b)}
+    ref = arms["single"]().clone()
+    same = {k: bool(torch.equal(arms[k](), ref)) for k in ("mc", "pair")}
+    times = {k: [] for k in arms}
+    for _ in range(rounds):
+        for k, fn in arms.items():
+            avg, _ = timeit(fn, iters=iters, warmup=1)
+            times[k].append(avg)
+    flops = 2.0 * M * N * K
+    rec = dict(kernel="gemm_sched_" + epi, shape=[M, N, K], bit_identical=same)
+    for k, ts in times.items():
+        ms = sum(ts) / len(ts)
+        rec[k] = dict(ms=ms, ms_min=min(ts), tflops=flops / ms / 1e9)
+    emit(rec)
+
+
 def bench_attn(B, H, Lq, Lk, variant):
     q = torch.randn(B, Lq, H, 128, device="cuda", dtype=torch.bfloat16)
     k = torch.randn(B, Lk, H, 128, device="cuda", dtype=torch.bfloat16)
@@ -170,6 +203,11 @@ if __name__ == "__main__":
         for (N, K, epi) in [(15360, 5120, "bias"), (5120, 5120, "gate_res"), (13824, 5120, "gelu"), (5120, 13824, "gate_res"),
                             (5120, 512, "bias"), (4608, 1536, "bias")]:
             bench_gemm(M, N, K, epi)
+    if "gemm_sched" in which:
+        for (M, N, K, epi) in [(65520, 15360, 5120, "bias"), (65520, 5120, 5120, "gate_res"), (65520, 13824, 5120, "gelu"),
+                               (65520, 5120, 13824, "gate_res"), (65520, 4608, 1536, "bias"), (65520, 8960, 1536, "gelu"),
+                               (65520, 1536, 8960, "gate_res"), (8190, 15360, 5120, "bias"), (8190, 5120, 13824, "gate_res")]:
+            bench_gemm_sched(M, N, K, epi)
     if "attn_sustained" in which:
         for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "1,2").split(",")]:
             bench_attn_sustained(variant)

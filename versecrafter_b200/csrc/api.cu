@@ -2,7 +2,9 @@
 // driver entry point (so the .so has no link-time libcuda dependency and loads on a machine without a GPU).
 #include <cstdarg>
 #include <cstdio>
+#include <cstring>
 #include <mutex>
+#include <unordered_map>
 
 #include "common.cuh"
 
@@ -48,12 +50,49 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
   return make_tmap(out, base, TMAP_BF16, TMAP_SWIZZLE_128B, rank, dims, strides_bytes, box);
 }
 
+// Encoded tensor maps are cached per host thread, keyed on everything cuTensorMapEncodeTiled sees (base address, element
+// type, swizzle, dims, strides, box): a denoise step re-launches the same ~40 (pointer, shape) combinations 931 times, and
+// a map only describes addresses and extents, so a hit is valid for as long as the caller's buffer is.
+namespace {
+struct TmapKey {
+  uint64_t v[17];
+  bool operator==(const TmapKey& o) const { return memcmp(v, o.v, sizeof(v)) == 0; }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    uint64_t h = 1469598103934665603ull;
+    for (uint64_t x : k.v) {
+      h ^= x;
+      h *= 1099511628211ull;
+    }
+    return (size_t)h;
+  }
+};
+thread_local std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
+constexpr size_t kTmapCacheMax = 8192;
+}  // namespace
+
 int make_tmap(CUtensorMap* out, const void* base, TmapDtype dtype, TmapSwizzle swizzle, int rank, const uint64_t* dims,
               const uint64_t* strides_bytes, const uint32_t* box) {
   std::call_once(g_encode_once, resolve_encode);
   if (!g_encode) {
     set_error("cuTensorMapEncodeTiled not available from the driver (no CUDA driver / GPU?)");
     return -2;
+  }
+  TmapKey key;
+  memset(key.v, 0, sizeof(key.v));
+  key.v[0] = reinterpret_cast<uint64_t>(base);
+  key.v[1] = ((uint64_t)dtype << 32) | ((uint64_t)swizzle << 16) | (uint64_t)rank;
+  for (int i = 0; i < rank; ++i) {
+    key.v[2 + i] = dims[i];
+    key.v[7 + i] = box[i];
+  }
+  for (int i = 0; i + 1 < rank; ++i) key.v[12 + i] = strides_bytes[i];
+  key.v[16] = (uint64_t)current_device();
+  auto hit = g_tmap_cache.find(key);
+  if (hit != g_tmap_cache.end()) {
+    *out = hit->second;
+    return 0;
   }
   cuuint64_t gdim[5];
   cuuint64_t gstr[4];
@@ -73,6 +112,8 @@ int make_tmap(CUtensorMap* out, const void* base, TmapDtype dtype, TmapSwizzle s
               (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)strides_bytes[0]);
     return 1000 + (int)r;
   }
+  if (g_tmap_cache.size() >= kTmapCacheMax) g_tmap_cache.clear();
+  g_tmap_cache.emplace(key, *out);
   return 0;
 }
 

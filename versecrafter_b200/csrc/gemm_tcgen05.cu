@@ -10,6 +10,7 @@
 // The accumulator is double-buffered in TMEM so tile i's epilogue overlaps tile i+1's main loop.
 // Epilogue rounding points follow the reference's op-by-op bf16 arithmetic.
 #include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 
@@ -22,8 +23,10 @@ constexpr int BAR_BYTES = 256;
 constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + BAR_BYTES + 1024;  // +1024 for manual alignment
 constexpr int GROUP_M = 16;
 constexpr int NUM_THREADS = 192;
+constexpr int DEFAULT_SCHED = 0;  // see vc_gemm_bf16: 0 single, 1 multicast cluster, 2 CTA pair
 
-enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16, SCHED_MULTICAST = 64 };
+enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16, SCHED_MULTICAST = 64, SCHED_PAIR = 128,
+             SCHED_SINGLE = 256 };
 
 struct GemmParams {
   long long M, N, K;
@@ -56,6 +59,82 @@ __device__ __forceinline__ float gelu_tanh(float x) {
   const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
   const float t = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * u));
   return 0.5f * x * (1.0f + t);
+}
+
+// Epilogue of one 128-row x 256-column accumulator tile: this thread owns TMEM lane (= tile row) quarter*32 + lane and walks
+// the columns 32 at a time: tcgen05.ld -> bias / GELU-tanh / gate / scale / residual (bf16 roundings as the reference's
+// op-by-op arithmetic) -> bf16 16-byte stores.  t_addr = TMEM address of the tile's first column
+// in this warp's lane quarter.
+template <int EPI>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t t_addr, int m, int n, int quarter, int lane) {
+  const long long row = (long long)m * BM + quarter * 32 + lane;
+  const bool row_ok = row < p.M;
+  __nv_bfloat16* crow = p.C + row * p.ldc;
+  const __nv_bfloat16* rrow = (EPI & EPI_RES) ? p.residual + row * p.ldr : nullptr;
+  const __nv_bfloat16* grow =
+      (EPI & EPI_GATE) ? p.gate + (row_ok ? row / p.rows_per_batch : 0) * p.gate_stride : nullptr;
+#pragma unroll 1
+  for (int c = 0; c < BN / 32; ++c) {
+    uint32_t r[32];
+    vc::tmem_ld32(t_addr + c * 32, r);
+    vc::tmem_ld_wait();
+    const long long col0 = (long long)n * BN + c * 32;
+    if (row_ok && col0 < p.N) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {  // 8 columns = one 16-byte store
+        const long long col = col0 + g * 8;
+        if (col < p.N) {
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+          if (EPI & EPI_BIAS) {
+            const uint4 bu = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
+            const float2 b0 = vc::unpack_bf16x2(bu.x), b1 = vc::unpack_bf16x2(bu.y), b2 = vc::unpack_bf16x2(bu.z),
+                         b3 = vc::unpack_bf16x2(bu.w);
+            v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
+            v[4] += b2.x; v[5] += b2.y; v[6] += b3.x; v[7] += b3.y;
+          }
+          if (EPI & (EPI_GELU | EPI_GATE | EPI_RES | EPI_SCALE)) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = vc::bf16_round(v[j]);  // the Linear's own bf16 output
+          }
+          if (EPI & EPI_GELU) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
+          }
+          if (EPI & EPI_GATE) {
+            const uint4 gu = __ldg(reinterpret_cast<const uint4*>(grow + col));
+            const float2 g0 = vc::unpack_bf16x2(gu.x), g1 = vc::unpack_bf16x2(gu.y), g2 = vc::unpack_bf16x2(gu.z),
+                         g3 = vc::unpack_bf16x2(gu.w);
+            v[0] *= g0.x; v[1] *= g0.y; v[2] *= g1.x; v[3] *= g1.y;
+            v[4] *= g2.x; v[5] *= g2.y; v[6] *= g3.x; v[7] *= g3.y;
+          }
+          if (EPI & EPI_SCALE) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] *= p.scale;
+          }
+          if (EPI & EPI_RES) {
+            const uint4 ru = *reinterpret_cast<const uint4*>(rrow + col);
+            const float2 r0 = vc::unpack_bf16x2(ru.x), r1 = vc::unpack_bf16x2(ru.y), r2 = vc::unpack_bf16x2(ru.z),
+                         r3 = vc::unpack_bf16x2(ru.w);
+            if (EPI & (EPI_GATE | EPI_SCALE)) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = vc::bf16_round(v[j]);  // y*gate (or hint*scale) rounds first
+            }
+            v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
+            v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
+          }
+          uint4 o;
+          o.x = vc::pack_bf16x2(v[0], v[1]);
+          o.y = vc::pack_bf16x2(v[2], v[3]);
+          o.z = vc::pack_bf16x2(v[4], v[5]);
+          o.w = vc::pack_bf16x2(v[6], v[7]);
+          if (p.l2_hint & 4) __stcs(reinterpret_cast<uint4*>(crow + col), o);
+          else *reinterpret_cast<uint4*>(crow + col) = o;
+        }
+      }
+    }
+  }
 }
 
 // kMC: the grid is launched as clusters of 2 CTAs that work on two vertically adjacent M tiles of the same N tile; each
@@ -181,75 +260,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (kMC) m = 2 * m + crank;  // may be one past the last M tile: loads are zero-filled, stores masked
       vc::mbar_wait(&acc_full[acc], acc_phase);
       vc::tc_fence_after();
-      const long long row = (long long)m * BM + quarter * 32 + lane;
-      const bool row_ok = row < p.M;
-      __nv_bfloat16* crow = p.C + row * p.ldc;
-      const __nv_bfloat16* rrow = (EPI & EPI_RES) ? p.residual + row * p.ldr : nullptr;
-      const __nv_bfloat16* grow =
-          (EPI & EPI_GATE) ? p.gate + (row_ok ? row / p.rows_per_batch : 0) * p.gate_stride : nullptr;
-      const uint32_t t_addr = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        vc::tmem_ld32(t_addr + c * 32, r);
-        vc::tmem_ld_wait();
-        const long long col0 = (long long)n * BN + c * 32;
-        if (row_ok && col0 < p.N) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {  // 8 columns = one 16-byte store
-            const long long col = col0 + g * 8;
-            if (col < p.N) {
-              float v[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
-              if (EPI & EPI_BIAS) {
-                const uint4 bu = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
-                const float2 b0 = vc::unpack_bf16x2(bu.x), b1 = vc::unpack_bf16x2(bu.y), b2 = vc::unpack_bf16x2(bu.z),
-                             b3 = vc::unpack_bf16x2(bu.w);
-                v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
-                v[4] += b2.x; v[5] += b2.y; v[6] += b3.x; v[7] += b3.y;
-              }
-              if (EPI & (EPI_GELU | EPI_GATE | EPI_RES | EPI_SCALE)) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = vc::bf16_round(v[j]);  // the Linear's own bf16 output
-              }
-              if (EPI & EPI_GELU) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
-              }
-              if (EPI & EPI_GATE) {
-                const uint4 gu = __ldg(reinterpret_cast<const uint4*>(grow + col));
-                const float2 g0 = vc::unpack_bf16x2(gu.x), g1 = vc::unpack_bf16x2(gu.y), g2 = vc::unpack_bf16x2(gu.z),
-                             g3 = vc::unpack_bf16x2(gu.w);
-                v[0] *= g0.x; v[1] *= g0.y; v[2] *= g1.x; v[3] *= g1.y;
-                v[4] *= g2.x; v[5] *= g2.y; v[6] *= g3.x; v[7] *= g3.y;
-              }
-              if (EPI & EPI_SCALE) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] *= p.scale;
-              }
-              if (EPI & EPI_RES) {
-                const uint4 ru = *reinterpret_cast<const uint4*>(rrow + col);
-                const float2 r0 = vc::unpack_bf16x2(ru.x), r1 = vc::unpack_bf16x2(ru.y), r2 = vc::unpack_bf16x2(ru.z),
-                             r3 = vc::unpack_bf16x2(ru.w);
-                if (EPI & (EPI_GATE | EPI_SCALE)) {
-#pragma unroll
-                  for (int j = 0; j < 8; ++j) v[j] = vc::bf16_round(v[j]);  // y*gate (or hint*scale) rounds first
-                }
-                v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
-                v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
-              }
-              uint4 o;
-              o.x = vc::pack_bf16x2(v[0], v[1]);
-              o.y = vc::pack_bf16x2(v[2], v[3]);
-              o.z = vc::pack_bf16x2(v[4], v[5]);
-              o.w = vc::pack_bf16x2(v[6], v[7]);
-              if (p.l2_hint & 4) __stcs(reinterpret_cast<uint4*>(crow + col), o);
-              else *reinterpret_cast<uint4*>(crow + col) = o;
-            }
-          }
-        }
-      }
+      epilogue_tile<EPI>(p, tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16), m, n, quarter, lane);
       vc::tc_fence_before();
       vc::mbar_arrive(&acc_empty[acc]);
       acc ^= 1;
@@ -261,6 +272,170 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   if (kMC) vc::cluster_sync();  // the peer may still multicast into this CTA's smem / arrive on its barriers
   if (warp == 2) vc::tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------------------------------------------------------------
+// CTA-pair variant (`tcgen05.mma.cta_group::2`, M = 256 per pair).  A cluster of two CTAs (the two SMs of one TPC) owns a
+// 256 x 256 output tile: CTA r holds rows [r*128, r*128+128) of the A tile and rows [r*128, ...) of the W tile (HALF of
+// it) per k-block, 32 KB per stage instead of 48 KB, so the ring is 6 deep; each SM's tensor core reads its own A rows and
+// both halves of W (the peer's half over the pair's shared-memory path) — the operand bytes each SM pulls out of shared
+// memory and out of L2 per flop drop by a third, which is the energy-per-flop lever on a power-capped chip.
+// Roles per CTA are those of the kernel above; only the leader (cluster rank 0) runs the MMA issuer.  Barriers:
+//   full[s]      leader's only: expect_tx of BOTH CTAs' bytes (64 KB); every TMA load of either CTA credits it
+//   empty[s]     one per CTA, count 1: the leader's tcgen05.commit multicasts the arrive to both producers
+//   acc_full[a]  one per CTA, count 1: multicast commit at the end of a tile's k loop -> both epilogues
+//   acc_empty[a] leader's only, count 256: the 128 epilogue threads of each CTA arrive (the peer's remotely)
+constexpr int STAGES2 = 6;
+constexpr int B2_BYTES = (BN / 2) * BK * 2;  // 16 KB: this CTA's half of the W tile
+constexpr int SMEM2_BYTES = STAGES2 * (A_BYTES + B2_BYTES) + BAR_BYTES + 1024;
+
+template <int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES2 * A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES2 * (A_BYTES + B2_BYTES));
+  uint64_t* empty = full + STAGES2;
+  uint64_t* acc_full = empty + STAGES2;
+  uint64_t* acc_empty = acc_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int crank = (int)vc::cluster_ctarank();
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES2; ++i) {
+      vc::mbar_init(&full[i], 1);
+      vc::mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      vc::mbar_init(&acc_full[i], 1);
+      vc::mbar_init(&acc_empty[i], 256);
+    }
+    vc::fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    vc::tma_prefetch_desc(&tmA);
+    vc::tma_prefetch_desc(&tmB);
+  }
+  if (warp == 2) vc::tmem_alloc_2cta(tmem_slot, 512);
+  vc::tc_fence_before();
+  __syncthreads();
+  vc::cluster_sync();  // both CTAs' barriers are initialised and both TMEM halves allocated before any cross-CTA signal
+  vc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int t_first = (int)(blockIdx.x >> 1), t_step = (int)(gridDim.x >> 1);
+  const int sched_m = (p.m_tiles + 1) / 2;
+  const int sched_g = max(p.group_m / 2, 1);
+  const int num_tiles = sched_m * p.n_tiles;
+  const int k_blocks = (int)((p.K + BK - 1) / BK);
+
+  if (warp == 0) {
+    // ------------------------------------------------ TMA producer (both CTAs: own A rows, own half of W)
+    if (vc::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint64_t pol_a = (p.l2_hint & 1) ? vc::L2_EVICT_LAST : vc::L2_EVICT_NORMAL;
+      const uint64_t pol_b = (p.l2_hint & 2) ? vc::L2_EVICT_FIRST : vc::L2_EVICT_NORMAL;
+      for (int t = t_first; t < num_tiles; t += t_step) {
+        int mp, n;
+        tile_coords(t, sched_m, p.n_tiles, sched_g, mp, n);
+        const int m = 2 * mp + crank;  // may be one past the last M tile: loads are zero-filled, stores masked
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          vc::mbar_wait(&empty[stage], phase ^ 1);
+          if (crank == 0) vc::mbar_expect_tx(&full[stage], 2 * (A_BYTES + B2_BYTES));
+          vc::tma_load_2d_2cta(sA + stage * A_BYTES, &tmA, &full[stage], kb * BK, m * BM, pol_a);
+          vc::tma_load_2d_2cta(sB + stage * B2_BYTES, &tmB, &full[stage], kb * BK, n * BN + crank * (BN / 2), pol_b);
+          if (++stage == STAGES2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------ MMA issuer (leader CTA only): M = 256, N = 256, K = 16
+    if (crank == 0 && vc::elect_one()) {
+      constexpr uint32_t idesc = vc::umma_idesc_bf16(2 * BM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = t_first; t < num_tiles; t += t_step) {
+        vc::mbar_wait_cluster(&acc_empty[acc], acc_phase ^ 1);
+        vc::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          vc::mbar_wait_cluster(&full[stage], phase);
+          vc::tc_fence_after();
+          const uint32_t a0 = vc::smem_u32(sA + stage * A_BYTES);
+          const uint32_t b0 = vc::smem_u32(sB + stage * B2_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            vc::umma_ss_2cta(d_tmem, vc::umma_desc_sw128(a0 + k * 32, 16, 1024), vc::umma_desc_sw128(b0 + k * 32, 16, 1024),
+                             idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          vc::umma_commit_2cta_mc(&empty[stage], (uint16_t)3);  // frees this stage in both CTAs when the MMAs retire
+          if (++stage == STAGES2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        vc::umma_commit_2cta_mc(&acc_full[acc], (uint16_t)3);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ------------------------------------------------ epilogue (warps 2..5 of both CTAs, each CTA its own 128 rows)
+    const int quarter = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = t_first; t < num_tiles; t += t_step) {
+      int mp, n;
+      tile_coords(t, sched_m, p.n_tiles, sched_g, mp, n);
+      const int m = 2 * mp + crank;
+      vc::mbar_wait_cluster(&acc_full[acc], acc_phase);
+      vc::tc_fence_after();
+      epilogue_tile<EPI>(p, tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16), m, n, quarter, lane);
+      vc::tc_fence_before();
+      vc::mbar_arrive_leader(&acc_empty[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  vc::tc_fence_before();
+  __syncthreads();
+  vc::cluster_sync();  // the leader's MMAs read the peer's shared memory and signal its barriers until the very end
+  if (warp == 2) vc::tmem_dealloc_2cta(tmem_base, 512);
+}
+
+template <int EPI>
+int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
+  VC_ENSURE_DYN_SMEM((gemm_bf16_2cta_kernel<EPI>), SMEM2_BYTES, "vc_gemm_bf16");
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = SMEM2_BYTES;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_bf16_2cta_kernel<EPI>, ta, tb, p);
+  if (e != cudaSuccess) {
+    vc_host::set_error("vc_gemm_bf16: CTA-pair launch failed: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  return 0;
 }
 
 template <int EPI, bool kMC>
@@ -290,9 +465,11 @@ int launch_impl(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& 
   return 0;
 }
 
+// sched: 0 = one CTA per tile, 1 = cluster of 2 sharing W by TMA multicast, 2 = CTA pair (cta_group::2, M = 256)
 template <int EPI>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, bool mc, cudaStream_t s) {
-  return mc ? launch_impl<EPI, true>(ta, tb, p, grid, s) : launch_impl<EPI, false>(ta, tb, p, grid, s);
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, int sched, cudaStream_t s) {
+  if (sched == 2) return launch_2cta<EPI>(ta, tb, p, grid, s);
+  return sched == 1 ? launch_impl<EPI, true>(ta, tb, p, grid, s) : launch_impl<EPI, false>(ta, tb, p, grid, s);
 }
 
 using vc_host::sm_count;
@@ -335,8 +512,20 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
 
   // VC_GEMM_MC=1 or the VC_GEMM_SCHED_MULTICAST bit: clusters of 2 CTAs sharing the W tile by TMA multicast (see the
   // kernel); needs >= 2 M tiles.  Same arithmetic, bit-identical results.
-  static const bool mc_env = []() { const char* e = getenv("VC_GEMM_MC"); return e && e[0] == '1'; }();
-  const bool mc = (mc_env || (epilogue & SCHED_MULTICAST)) && M > BM;
+  // Schedule (same arithmetic, bit-identical results): 0 = one CTA per 128x256 tile; 1 = cluster of 2 sharing the W tile by
+  // TMA multicast; 2 = CTA pair, one cta_group::2 MMA of M = 256 per pair.  Chosen by the VC_GEMM_SCHED_* bits of
+  // `epilogue`, else VC_GEMM_SCHED = single | mc | pair (VC_GEMM_MC=1 is the older spelling of mc), else the default.
+  static const int sched_env = []() {
+    const char* e = getenv("VC_GEMM_SCHED");
+    if (e && !strcmp(e, "single")) return 0;
+    if (e && !strcmp(e, "mc")) return 1;
+    if (e && !strcmp(e, "pair")) return 2;
+    const char* m = getenv("VC_GEMM_MC");
+    return (m && m[0] == '1') ? 1 : DEFAULT_SCHED;
+  }();
+  int sched = (epilogue & SCHED_SINGLE) ? 0 : (epilogue & SCHED_PAIR) ? 2 : (epilogue & SCHED_MULTICAST) ? 1 : sched_env;
+  if (M <= BM) sched = 0;  // the paired schedules need two M tiles
+  const bool mc = sched != 0;
   CUtensorMap ta, tb;
   {
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
@@ -391,13 +580,13 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   }
   cudaStream_t s = (cudaStream_t)stream;
   int rc;
-  switch (epilogue & ~SCHED_MULTICAST) {
-    case 0: rc = launch<0>(ta, tb, p, grid, mc, s); break;
-    case EPI_BIAS: rc = launch<EPI_BIAS>(ta, tb, p, grid, mc, s); break;
-    case EPI_BIAS | EPI_GELU: rc = launch<EPI_BIAS | EPI_GELU>(ta, tb, p, grid, mc, s); break;
-    case EPI_BIAS | EPI_RES: rc = launch<EPI_BIAS | EPI_RES>(ta, tb, p, grid, mc, s); break;
-    case EPI_BIAS | EPI_GATE | EPI_RES: rc = launch<EPI_BIAS | EPI_GATE | EPI_RES>(ta, tb, p, grid, mc, s); break;
-    case EPI_BIAS | EPI_SCALE | EPI_RES: rc = launch<EPI_BIAS | EPI_SCALE | EPI_RES>(ta, tb, p, grid, mc, s); break;
+  switch (epilogue & ~(SCHED_MULTICAST | SCHED_PAIR | SCHED_SINGLE)) {
+    case 0: rc = launch<0>(ta, tb, p, grid, sched, s); break;
+    case EPI_BIAS: rc = launch<EPI_BIAS>(ta, tb, p, grid, sched, s); break;
+    case EPI_BIAS | EPI_GELU: rc = launch<EPI_BIAS | EPI_GELU>(ta, tb, p, grid, sched, s); break;
+    case EPI_BIAS | EPI_RES: rc = launch<EPI_BIAS | EPI_RES>(ta, tb, p, grid, sched, s); break;
+    case EPI_BIAS | EPI_GATE | EPI_RES: rc = launch<EPI_BIAS | EPI_GATE | EPI_RES>(ta, tb, p, grid, sched, s); break;
+    case EPI_BIAS | EPI_SCALE | EPI_RES: rc = launch<EPI_BIAS | EPI_SCALE | EPI_RES>(ta, tb, p, grid, sched, s); break;
     default:
       vc_host::set_error("vc_gemm_bf16: unsupported epilogue mask %d", epilogue);
       return -1;

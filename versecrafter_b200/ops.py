@@ -8,7 +8,9 @@ import torch
 from . import _lib
 
 EPI_BIAS, EPI_GELU, EPI_GATE, EPI_RES, EPI_SCALE = 1, 2, 4, 8, 16
-SCHED_MULTICAST = 64   # schedule bit of vc_gemm_bf16: cluster-of-2 TMA-multicast variant (same arithmetic)
+SCHED_MULTICAST = 64   # schedule bits of vc_gemm_bf16 (same arithmetic): cluster of 2 sharing W by TMA multicast,
+SCHED_PAIR = 128       # CTA pair issuing one cta_group::2 MMA of M = 256,
+SCHED_SINGLE = 256     # one CTA per tile (overrides the VC_GEMM_SCHED default)
 
 # kernels launched through this module since the last reset (bench.py reports it as gpu_launches)
 launch_count = 0
