@@ -78,18 +78,45 @@ def test_bf16_oracle_matches_the_reference_under_autocast(ref_mods, name):
     # embeddings and the fp32 time-MLP island
     assert relerr(rec["e0"], cap["e0"]) < 1e-3, relerr(rec["e0"], cap["e0"])
     assert relerr(rec["ctx"], cap["ctx"]) < 2e-3
-    # every block, free-running in both (drift of two bf16 evaluations of the same op sequence)
+    # patch embedding: the reference runs cuDNN's Conv3d, the oracle the equivalent GEMM — same arithmetic, different
+    # fp32 summation order, so individual outputs differ by one bf16 ulp
+    x0_err = relerr(rec["x0"], cap["blk_in.0"])
+    assert x0_err < 4e-3, x0_err
+    # every block TEACHER-FORCED: the oracle's block on the very input (and e0 / text context) the reference's block saw
+    H = cfg["num_heads"]
+    gridp = (grid[0], grid[1] // 2, grid[2] // 2)
+    ang = restate.rope_angles(cfg["dim"] // H, gridp, device="cuda")
+    n_geo = len(cfg.get("geoada_layers") or range(0, cfg["num_layers"], 2))
+    if cap["attention_impl"] == "flash_attn":
+        restate.set_attention_impl("flash")
+    try:
+        tf = {}
+        for i in range(cfg["num_layers"]):
+            got = restate.dit_block(r["sd"], f"blocks.{i}.", cap[f"blk_in.{i}"], cap["e0"], ang, cap["ctx"], H)
+            tf[f"blocks.{i}"] = relerr(got, cap[f"blk_core.{i}"])
+        for j in range(n_geo):
+            got = restate.dit_block(r["sd"], f"geoada_blocks.{j}.", cap[f"geo_in.{j}"], cap["e0"], ang, cap["ctx"], H)
+            tf[f"geoada_blocks.{j}"] = relerr(got, cap[f"geo_out.{j}"])
+            hint = restate.linear(cap[f"geo_out.{j}"], r["sd"][f"geoada_blocks.{j}.after_proj.weight"],
+                                  r["sd"][f"geoada_blocks.{j}.after_proj.bias"])
+            tf[f"hint.{j}"] = relerr(hint, cap[f"hint.{j}"])
+    finally:
+        restate.set_attention_impl("sdpa")
+    worst_tf = max(tf.values())
+    # free-running (the one-ulp embedding differences propagate through the blocks: bf16-noise level drift)
     worst = 0.0
     for i in range(cfg["num_layers"]):
         worst = max(worst, relerr(rec[f"blk_out.{i}"], cap[f"blk_out.{i}"]))
-    for j in range(len(cfg.get("geoada_layers") or range(0, cfg["num_layers"], 2))):
+    for j in range(n_geo):
         worst = max(worst, relerr(rec[f"geo_out.{j}"], cap[f"geo_out.{j}"]), relerr(rec[f"hint.{j}"], cap[f"hint.{j}"]))
     _log(dict(test="bf16_oracle_vs_reference_autocast", case=name, attention=cap["attention_impl"],
+              teacher_forced_block_rel_l2=tf, worst_teacher_forced=worst_tf, x0_rel_l2=x0_err,
               final_rel_l2=relerr(y16, r["y"]), final_cosine=cosine(y16, r["y"]), worst_free_running_block_rel_l2=worst,
               e0_rel_l2=relerr(rec["e0"], cap["e0"]), ctx_rel_l2=relerr(rec["ctx"], cap["ctx"]),
               bit_identical=bool(torch.equal(y16, r["y"]))))
-    assert worst < 6e-3, worst
-    assert relerr(y16, r["y"]) < 6e-3 and cosine(y16, r["y"]) > 0.99995
+    assert worst_tf < 1e-3, tf              # op-for-op agreement of the bf16 restatement with the reference under autocast
+    assert worst < 1e-2, worst
+    assert relerr(y16, r["y"]) < 1e-2 and cosine(y16, r["y"]) > 0.9999
 
 
 @pytest.mark.parametrize("name", sorted(CASES))

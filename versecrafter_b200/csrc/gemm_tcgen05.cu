@@ -6,7 +6,8 @@
 //   warp 0   : TMA producer  (A tile 128x64, W tile 256x64, 128B swizzle, 4-stage mbarrier ring)
 //   warp 1   : one elected thread issues tcgen05.mma M=128 N=256 K=16 (4 per k-block), fp32 accumulators in TMEM
 //   warp 2   : TMEM allocator (512 columns = 2 accumulator stages of 256) + epilogue
-//   warps 2-5: epilogue: tcgen05.ld 32 columns at a time -> bias / GELU-tanh / gate / scale / residual -> bf16 global
+//   warps 2-9: epilogue (lane quarter = warp % 4, column half = (warp - 2) / 4): tcgen05.ld 32 columns at a time,
+//              software-pipelined -> bias / GELU-tanh / gate / scale / residual -> bf16 global
 // The accumulator is double-buffered in TMEM so tile i's epilogue overlaps tile i+1's main loop.
 // Epilogue rounding points follow the reference's op-by-op bf16 arithmetic.
 #include <cstdlib>
@@ -22,7 +23,8 @@ constexpr int B_BYTES = BN * BK * 2;  // 32 KB
 constexpr int BAR_BYTES = 256;
 constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + BAR_BYTES + 1024;  // +1024 for manual alignment
 constexpr int GROUP_M = 16;
-constexpr int NUM_THREADS = 192;
+constexpr int EPI_WARPS = 8;
+constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;  // TMA warp, MMA warp, epilogue warps
 constexpr int DEFAULT_SCHED = 0;  // see vc_gemm_bf16: 0 single, 1 multicast cluster, 2 CTA pair
 
 enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16, SCHED_MULTICAST = 64, SCHED_PAIR = 128,
@@ -61,79 +63,94 @@ __device__ __forceinline__ float gelu_tanh(float x) {
   return 0.5f * x * (1.0f + t);
 }
 
-// Epilogue of one 128-row x 256-column accumulator tile: this thread owns TMEM lane (= tile row) quarter*32 + lane and walks
-// the columns 32 at a time: tcgen05.ld -> bias / GELU-tanh / gate / scale / residual (bf16 roundings as the reference's
-// op-by-op arithmetic) -> bf16 16-byte stores.  t_addr = TMEM address of the tile's first column
-// in this warp's lane quarter.
+// Epilogue of one 128-row x 256-column accumulator tile, split over EPI_WARPS = 8 warps: warp w owns TMEM lane quarter
+// w % 4 (= tile rows quarter*32 .. +31, one row per thread) and column half (w - 2) / 4 (128 columns = 4 chunks of 32).
+// Per chunk: tcgen05.ld -> bias / GELU-tanh / gate / scale / residual (bf16 roundings as the reference's op-by-op
+// arithmetic) -> bf16 16-byte stores; the next chunk's tcgen05.ld is in flight during the math.
+// (Round 1 used 4 warps x 8 chunks with the load waited for immediately: at K = 1536 the epilogue of a tile then took
+// longer than its 24 k-blocks of MMAs and the kernel fell to 0.71 of the bf16 peak, below cuBLASLt.)
 template <int EPI>
-__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t t_addr, int m, int n, int quarter, int lane) {
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32_t* r, long long col0, bool row_ok,
+                                               __nv_bfloat16* crow, const __nv_bfloat16* rrow, const __nv_bfloat16* grow) {
+  if (row_ok && col0 < p.N) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {  // 8 columns = one 16-byte store
+      const long long col = col0 + g * 8;
+      if (col < p.N) {
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+        if (EPI & EPI_BIAS) {
+          const uint4 bu = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
+          const float2 b0 = vc::unpack_bf16x2(bu.x), b1 = vc::unpack_bf16x2(bu.y), b2 = vc::unpack_bf16x2(bu.z),
+                       b3 = vc::unpack_bf16x2(bu.w);
+          v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
+          v[4] += b2.x; v[5] += b2.y; v[6] += b3.x; v[7] += b3.y;
+        }
+        if (EPI & (EPI_GELU | EPI_GATE | EPI_RES | EPI_SCALE)) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = vc::bf16_round(v[j]);  // the Linear's own bf16 output
+        }
+        if (EPI & EPI_GELU) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
+        }
+        if (EPI & EPI_GATE) {
+          const uint4 gu = __ldg(reinterpret_cast<const uint4*>(grow + col));
+          const float2 g0 = vc::unpack_bf16x2(gu.x), g1 = vc::unpack_bf16x2(gu.y), g2 = vc::unpack_bf16x2(gu.z),
+                       g3 = vc::unpack_bf16x2(gu.w);
+          v[0] *= g0.x; v[1] *= g0.y; v[2] *= g1.x; v[3] *= g1.y;
+          v[4] *= g2.x; v[5] *= g2.y; v[6] *= g3.x; v[7] *= g3.y;
+        }
+        if (EPI & EPI_SCALE) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] *= p.scale;
+        }
+        if (EPI & EPI_RES) {
+          const uint4 ru = *reinterpret_cast<const uint4*>(rrow + col);
+          const float2 r0 = vc::unpack_bf16x2(ru.x), r1 = vc::unpack_bf16x2(ru.y), r2 = vc::unpack_bf16x2(ru.z),
+                       r3 = vc::unpack_bf16x2(ru.w);
+          if (EPI & (EPI_GATE | EPI_SCALE)) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = vc::bf16_round(v[j]);  // y*gate (or hint*scale) rounds first
+          }
+          v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
+          v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
+        }
+        uint4 o;
+        o.x = vc::pack_bf16x2(v[0], v[1]);
+        o.y = vc::pack_bf16x2(v[2], v[3]);
+        o.z = vc::pack_bf16x2(v[4], v[5]);
+        o.w = vc::pack_bf16x2(v[6], v[7]);
+        if (p.l2_hint & 4) __stcs(reinterpret_cast<uint4*>(crow + col), o);
+        else *reinterpret_cast<uint4*>(crow + col) = o;
+      }
+    }
+  }
+}
+
+template <int EPI>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t t_addr, int m, int n, int quarter, int half,
+                                              int lane) {
   const long long row = (long long)m * BM + quarter * 32 + lane;
   const bool row_ok = row < p.M;
   __nv_bfloat16* crow = p.C + row * p.ldc;
   const __nv_bfloat16* rrow = (EPI & EPI_RES) ? p.residual + row * p.ldr : nullptr;
   const __nv_bfloat16* grow =
       (EPI & EPI_GATE) ? p.gate + (row_ok ? row / p.rows_per_batch : 0) * p.gate_stride : nullptr;
-#pragma unroll 1
-  for (int c = 0; c < BN / 32; ++c) {
-    uint32_t r[32];
-    vc::tmem_ld32(t_addr + c * 32, r);
+  constexpr int CHUNKS = BN / 32 / 2;  // per warp
+  const int c0 = half * CHUNKS;
+  const long long colbase = (long long)n * BN + c0 * 32;
+  uint32_t ra[32], rb[32];
+  vc::tmem_ld32(t_addr + c0 * 32, ra);
+#pragma unroll
+  for (int c = 0; c < CHUNKS; c += 2) {
     vc::tmem_ld_wait();
-    const long long col0 = (long long)n * BN + c * 32;
-    if (row_ok && col0 < p.N) {
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {  // 8 columns = one 16-byte store
-        const long long col = col0 + g * 8;
-        if (col < p.N) {
-          float v[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
-          if (EPI & EPI_BIAS) {
-            const uint4 bu = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
-            const float2 b0 = vc::unpack_bf16x2(bu.x), b1 = vc::unpack_bf16x2(bu.y), b2 = vc::unpack_bf16x2(bu.z),
-                         b3 = vc::unpack_bf16x2(bu.w);
-            v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
-            v[4] += b2.x; v[5] += b2.y; v[6] += b3.x; v[7] += b3.y;
-          }
-          if (EPI & (EPI_GELU | EPI_GATE | EPI_RES | EPI_SCALE)) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = vc::bf16_round(v[j]);  // the Linear's own bf16 output
-          }
-          if (EPI & EPI_GELU) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
-          }
-          if (EPI & EPI_GATE) {
-            const uint4 gu = __ldg(reinterpret_cast<const uint4*>(grow + col));
-            const float2 g0 = vc::unpack_bf16x2(gu.x), g1 = vc::unpack_bf16x2(gu.y), g2 = vc::unpack_bf16x2(gu.z),
-                         g3 = vc::unpack_bf16x2(gu.w);
-            v[0] *= g0.x; v[1] *= g0.y; v[2] *= g1.x; v[3] *= g1.y;
-            v[4] *= g2.x; v[5] *= g2.y; v[6] *= g3.x; v[7] *= g3.y;
-          }
-          if (EPI & EPI_SCALE) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] *= p.scale;
-          }
-          if (EPI & EPI_RES) {
-            const uint4 ru = *reinterpret_cast<const uint4*>(rrow + col);
-            const float2 r0 = vc::unpack_bf16x2(ru.x), r1 = vc::unpack_bf16x2(ru.y), r2 = vc::unpack_bf16x2(ru.z),
-                         r3 = vc::unpack_bf16x2(ru.w);
-            if (EPI & (EPI_GATE | EPI_SCALE)) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = vc::bf16_round(v[j]);  // y*gate (or hint*scale) rounds first
-            }
-            v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
-            v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
-          }
-          uint4 o;
-          o.x = vc::pack_bf16x2(v[0], v[1]);
-          o.y = vc::pack_bf16x2(v[2], v[3]);
-          o.z = vc::pack_bf16x2(v[4], v[5]);
-          o.w = vc::pack_bf16x2(v[6], v[7]);
-          if (p.l2_hint & 4) __stcs(reinterpret_cast<uint4*>(crow + col), o);
-          else *reinterpret_cast<uint4*>(crow + col) = o;
-        }
-      }
-    }
+    vc::tmem_ld32(t_addr + (c0 + c + 1) * 32, rb);
+    epilogue_chunk<EPI>(p, ra, colbase + c * 32, row_ok, crow, rrow, grow);
+    vc::tmem_ld_wait();
+    if (c + 2 < CHUNKS) vc::tmem_ld32(t_addr + (c0 + c + 2) * 32, ra);
+    epilogue_chunk<EPI>(p, rb, colbase + (c + 1) * 32, row_ok, crow, rrow, grow);
   }
 }
 
@@ -164,7 +181,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int i = 0; i < 2; ++i) {
       vc::mbar_init(&acc_full[i], 1);
-      vc::mbar_init(&acc_empty[i], 128);
+      vc::mbar_init(&acc_empty[i], 32 * EPI_WARPS);
     }
     vc::fence_barrier_init();
   }
@@ -250,7 +267,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else {
-    // ------------------------------------------------ epilogue (warps 2..5 -> TMEM lane quarters 2,3,0,1)
+    // ------------------------------------------------ epilogue (warps 2..9 -> TMEM lane quarters 2,3,0,1,2,3,0,1)
     const int quarter = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -260,7 +277,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (kMC) m = 2 * m + crank;  // may be one past the last M tile: loads are zero-filled, stores masked
       vc::mbar_wait(&acc_full[acc], acc_phase);
       vc::tc_fence_after();
-      epilogue_tile<EPI>(p, tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16), m, n, quarter, lane);
+      epilogue_tile<EPI>(p, tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16), m, n, quarter, (warp - 2) >> 2,
+                         lane);
       vc::tc_fence_before();
       vc::mbar_arrive(&acc_empty[acc]);
       acc ^= 1;
@@ -284,7 +302,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 //   full[s]      leader's only: expect_tx of BOTH CTAs' bytes (64 KB); every TMA load of either CTA credits it
 //   empty[s]     one per CTA, count 1: the leader's tcgen05.commit multicasts the arrive to both producers
 //   acc_full[a]  one per CTA, count 1: multicast commit at the end of a tile's k loop -> both epilogues
-//   acc_empty[a] leader's only, count 256: the 128 epilogue threads of each CTA arrive (the peer's remotely)
+//   acc_empty[a] leader's only, count 512: the 256 epilogue threads of each CTA arrive (the peer's remotely)
 constexpr int STAGES2 = 6;
 constexpr int B2_BYTES = (BN / 2) * BK * 2;  // 16 KB: this CTA's half of the W tile
 constexpr int SMEM2_BYTES = STAGES2 * (A_BYTES + B2_BYTES) + BAR_BYTES + 1024;
@@ -313,7 +331,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     }
     for (int i = 0; i < 2; ++i) {
       vc::mbar_init(&acc_full[i], 1);
-      vc::mbar_init(&acc_empty[i], 256);
+      vc::mbar_init(&acc_empty[i], 2 * 32 * EPI_WARPS);
     }
     vc::fence_barrier_init();
   }
@@ -391,7 +409,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       }
     }
   } else {
-    // ------------------------------------------------ epilogue (warps 2..5 of both CTAs, each CTA its own 128 rows)
+    // ------------------------------------------------ epilogue (warps 2..9 of both CTAs, each CTA its own 128 rows)
     const int quarter = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -401,7 +419,8 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const int m = 2 * mp + crank;
       vc::mbar_wait_cluster(&acc_full[acc], acc_phase);
       vc::tc_fence_after();
-      epilogue_tile<EPI>(p, tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16), m, n, quarter, lane);
+      epilogue_tile<EPI>(p, tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16), m, n, quarter, (warp - 2) >> 2,
+                         lane);
       vc::tc_fence_before();
       vc::mbar_arrive_leader(&acc_empty[acc]);
       acc ^= 1;

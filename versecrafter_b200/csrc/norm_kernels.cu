@@ -7,6 +7,7 @@
 // one HBM write per element), 16-byte vector accesses, warp-shuffle reductions, no shared memory.
 // bf16 rounding points follow the reference's op-by-op autocast arithmetic.
 #include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 
@@ -428,6 +429,199 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_block_k
 }
 
 // ----------------------------------------------------------------------------------------------------
+// Row kernels with an asynchronous row ring (round 2).  ncu on the register-resident kernels above (profiles/
+// ncu_ln_r01j_summary.txt): 28 % warps active, 49 % issue-active, long-scoreboard bound — one 10 KB row per CTA does not
+// keep enough HBM reads in flight once the power cap drops the clock.  Here a CTA keeps RING rows of input in flight in
+// shared memory: one thread issues 1-D bulk copies (cp.async.bulk, the TMA engine) two rows ahead of the row being
+// reduced; the 128 threads pick their 16-byte vectors out of shared memory when the row's mbarrier completes.  Arithmetic
+// and rounding points are those of the kernels above (same helpers), so results are bit-identical.
+// ----------------------------------------------------------------------------------------------------
+constexpr int RING = 3;
+
+template <int VPT>
+__global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 2) ln_modulate_ring_kernel(
+    const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ p0,
+    const __nv_bfloat16* __restrict__ p1, long long mod_stride, long long rows, long long rows_per_batch, int D,
+    long long ldx, long long ldo, float eps, int mode) {
+  extern __shared__ __align__(16) uint8_t ring_smem[];
+  __shared__ float red_a[ROW_NT / 32], red_b[ROW_NT / 32];
+  __shared__ __align__(8) uint64_t full[RING];
+  const int nvec = D >> 3;
+  const uint32_t row_bytes = (uint32_t)D * 2;
+  const float inv_d = 1.0f / (float)D;
+  const long long my_rows = rows > (long long)blockIdx.x ? (rows - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < RING; ++i) vc::mbar_init(&full[i], 1);
+    vc::fence_barrier_init();
+    for (int i = 0; i < RING - 1 && i < my_rows; ++i) {
+      vc::mbar_expect_tx(&full[i], row_bytes);
+      vc::bulk_load_1d(ring_smem + (size_t)i * row_bytes, x + ((long long)blockIdx.x + (long long)i * gridDim.x) * ldx, row_bytes,
+                       &full[i]);
+    }
+  }
+  __syncthreads();
+  uint4 raw[VPT], sc[VPT], sh[VPT];
+  long long cached_batch = -1;
+  for (long long it = 0; it < my_rows; ++it) {
+    const long long row = (long long)blockIdx.x + it * gridDim.x;
+    const int slot = (int)(it % RING);
+    // refill the slot consumed in the previous iteration (every thread copied it to registers before that iteration's
+    // first __syncthreads) with the row RING-1 ahead
+    if (threadIdx.x == 0 && it + RING - 1 < my_rows) {
+      const int ns = (int)((it + RING - 1) % RING);
+      vc::mbar_expect_tx(&full[ns], row_bytes);
+      vc::bulk_load_1d(ring_smem + (size_t)ns * row_bytes, x + (row + (long long)(RING - 1) * gridDim.x) * ldx, row_bytes,
+                       &full[ns]);
+    }
+    const long long batch = (mode == 0) ? row / rows_per_batch : 0;
+    if (batch != cached_batch) {
+      cached_batch = batch;
+      const uint4* q0 = reinterpret_cast<const uint4*>(p0 + batch * mod_stride);
+      const uint4* q1 = reinterpret_cast<const uint4*>(p1 + batch * mod_stride);
+      const __nv_bfloat162 one2 = __floats2bfloat162_rn(1.0f, 1.0f);
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + ROW_NT * i;
+        if (v < nvec) {
+          sh[i] = __ldg(q0 + v);
+          uint4 c = __ldg(q1 + v);
+          if (mode == 0) {
+            c.x = as_u32(__hadd2_rn(one2, as_bf162(c.x)));
+            c.y = as_u32(__hadd2_rn(one2, as_bf162(c.y)));
+            c.z = as_u32(__hadd2_rn(one2, as_bf162(c.z)));
+            c.w = as_u32(__hadd2_rn(one2, as_bf162(c.w)));
+          }
+          sc[i] = c;
+        }
+      }
+    }
+    vc::mbar_wait(&full[slot], (uint32_t)((it / RING) & 1));
+    const uint4* xr = reinterpret_cast<const uint4*>(ring_smem + (size_t)slot * row_bytes);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + ROW_NT * i;
+      raw[i] = (v < nvec) ? xr[v] : make_uint4(0, 0, 0, 0);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) s += vec_sum(raw[i]);
+    const float mean = block_sum(s, red_a) * inv_d;
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      if (threadIdx.x + ROW_NT * i < nvec) ss = vec_sumsq(raw[i], mean, ss);
+    }
+    const float rstd = rsqrtf(block_sum(ss, red_b) * inv_d + eps);
+    uint4* orow = reinterpret_cast<uint4*>(out + row * ldo);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + ROW_NT * i;
+      if (v < nvec) {
+        const uint32_t xw[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
+        const uint32_t cw[4] = {sc[i].x, sc[i].y, sc[i].z, sc[i].w};
+        const uint32_t aw[4] = {sh[i].x, sh[i].y, sh[i].z, sh[i].w};
+        uint32_t ow[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float2 f = up2(xw[q]);
+          const float l0 = (f.x - mean) * rstd, l1 = (f.y - mean) * rstd;
+          if (mode == 0) {
+            ow[q] = as_u32(__hadd2_rn(__hmul2_rn(__floats2bfloat162_rn(l0, l1), as_bf162(cw[q])), as_bf162(aw[q])));
+          } else {
+            const float2 g = up2(cw[q]), bb = up2(aw[q]);
+            ow[q] = vc::pack_bf16x2(fmaf(l0, g.x, bb.x), fmaf(l1, g.y, bb.y));
+          }
+        }
+        st_stream(orow + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
+      }
+    }
+  }
+}
+
+// RMSNorm (+ RoPE) in place with the same ring; a ring entry is one (row, q|k) segment of D elements.
+template <int VPT>
+__global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_ring_kernel(
+    __nv_bfloat16* __restrict__ qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset, int D,
+    const __nv_bfloat16* __restrict__ gq, const __nv_bfloat16* __restrict__ gk, const float2* __restrict__ tab, int Fg,
+    int Hg, int Wg, int nf, int nh, int nw, float eps, int do_rope, int n_mats) {
+  extern __shared__ __align__(16) uint8_t ring_smem[];
+  __shared__ float red_a[ROW_NT / 32], red_b[ROW_NT / 32];
+  __shared__ __align__(8) uint64_t full[RING];
+  const int nvec = D >> 3;
+  const uint32_t row_bytes = (uint32_t)D * 2;
+  const float inv_d = 1.0f / (float)D;
+  const int half_d = nf + nh + nw;
+  const float2* tab_f = tab;
+  const float2* tab_h = tab + (long long)Fg * nf;
+  const float2* tab_w = tab_h + (long long)Hg * nh;
+  const int j0 = do_rope ? (((threadIdx.x * 8) % (2 * half_d)) >> 1) : 0;
+  const long long my_rows = rows > (long long)blockIdx.x ? (rows - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const long long my_segs = my_rows * n_mats;
+  // segment g of this CTA -> global address
+  auto seg_ptr = [&](long long g) {
+    const long long r = (long long)blockIdx.x + (g / n_mats) * gridDim.x;
+    return qkv + r * ld + (g % n_mats) * (long long)D;
+  };
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < RING; ++i) vc::mbar_init(&full[i], 1);
+    vc::fence_barrier_init();
+    for (int i = 0; i < RING - 1 && i < my_segs; ++i) {
+      vc::mbar_expect_tx(&full[i], row_bytes);
+      vc::bulk_load_1d(ring_smem + (size_t)i * row_bytes, seg_ptr(i), row_bytes, &full[i]);
+    }
+  }
+  __syncthreads();
+  uint4 raw[VPT];
+  float2 cs[4];
+  bool rot = false;
+  for (long long g = 0; g < my_segs; ++g) {
+    const int which = (int)(g % n_mats);
+    const long long row = (long long)blockIdx.x + (g / n_mats) * gridDim.x;
+    const int slot = (int)(g % RING);
+    if (threadIdx.x == 0 && g + RING - 1 < my_segs) {
+      const int ns = (int)((g + RING - 1) % RING);
+      vc::mbar_expect_tx(&full[ns], row_bytes);
+      vc::bulk_load_1d(ring_smem + (size_t)ns * row_bytes, seg_ptr(g + RING - 1), row_bytes, &full[ns]);
+    }
+    if (which == 0) {
+      const long long pos = pos_offset + (row % rows_per_batch);
+      rot = do_rope && pos < (long long)Fg * Hg * Wg;
+      if (rot) {
+        const int pw = (int)(pos % Wg);
+        const int ph = (int)((pos / Wg) % Hg);
+        const int pf = (int)(pos / ((long long)Wg * Hg));
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          const int j = j0 + p;
+          if (j < nf) cs[p] = __ldg(tab_f + pf * nf + j);
+          else if (j < nf + nh) cs[p] = __ldg(tab_h + ph * nh + (j - nf));
+          else cs[p] = __ldg(tab_w + pw * nw + (j - nf - nh));
+        }
+      }
+    }
+    vc::mbar_wait(&full[slot], (uint32_t)((g / RING) & 1));
+    const uint4* xs = reinterpret_cast<const uint4*>(ring_smem + (size_t)slot * row_bytes);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + ROW_NT * i;
+      raw[i] = (v < nvec) ? xs[v] : make_uint4(0, 0, 0, 0);
+    }
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) ss = vec_sumsq0(raw[i], ss);
+    const float r = rsqrtf(block_sum(ss, (g & 1) ? red_b : red_a) * inv_d + eps);
+    const __nv_bfloat162 r2 = __floats2bfloat162_rn(r, r);
+    uint4* xr = reinterpret_cast<uint4*>(qkv + row * ld + (long long)which * D);
+    const uint4* gr = reinterpret_cast<const uint4*>(which == 0 ? gq : gk);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + ROW_NT * i;
+      if (v < nvec) st_stream(xr + v, rms_rope_vec(raw[i], r2, __ldg(gr + v), rot, cs));
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------
 // Ulysses producer: RMSNorm + RoPE of q and k (as above) and a pass-through of v, with the
 // result STORED DIRECTLY INTO THE RECEIVE BUFFERS OF THE PEER GPUs over NVLink (peer-mapped pointers) instead of
 // in place: rank p receives heads [p*Hp, (p+1)*Hp) of every token.  Destination layout at each peer:
@@ -586,6 +780,11 @@ int grid_for_block_rows(long long rows) {
   return (int)(rows < cap ? (rows < 1 ? 1 : rows) : cap);
 }
 
+int grid_for_ring_rows(long long rows, int ctas_per_sm) {  // persistent: every resident CTA walks rows blockIdx.x + i*grid
+  const long long cap = (long long)vc_host::sm_count() * ctas_per_sm;
+  return (int)(rows < cap ? (rows < 1 ? 1 : rows) : cap);
+}
+
 int grid_for_rows(long long rows, int warps_per_cta) {
   long long ctas = (rows + warps_per_cta - 1) / warps_per_cta;
   const long long cap = 148LL * 8;  // 8 resident 256-thread CTAs per SM
@@ -602,8 +801,25 @@ int vc_ln_modulate(const void* x, long long ldx, void* out, long long ldo, const
   VC_CHECK_ARG(x && out && shift_or_beta && scale_or_gamma, "vc_ln_modulate: null pointer");
   VC_CHECK_ARG(D > 0 && D % 8 == 0 && D <= 8192, "vc_ln_modulate: D=%d must be a multiple of 8 and <= 8192", D);
   VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && ldx % 8 == 0 && ldo % 8 == 0, "vc_ln_modulate: bad rows/strides");
+  const bool force_regs = (mode & 16) != 0;  // VC_ROWS_REGS schedule bit: the register-resident kernel (A/B, tests)
+  mode &= ~16;
   VC_CHECK_ARG(mode == 0 || mode == 1, "vc_ln_modulate: mode must be 0 (modulate) or 1 (affine)");
   if (rows == 0) return 0;
+  // VC_ROW_KERNELS = ring (default: asynchronous row ring, cp.async.bulk) | regs (round-1 register-resident kernels)
+  static const bool use_ring = []() { const char* e = getenv("VC_ROW_KERNELS"); return !(e && !strcmp(e, "regs")); }();
+  if (D > 1024 && use_ring && !force_regs && reinterpret_cast<uintptr_t>(x) % 16 == 0) {
+    int rcb = dispatch_vpt(D, [&](auto vpt) {
+      constexpr int V = decltype(vpt)::value;
+      const int smem = RING * D * 2;
+      VC_ENSURE_DYN_SMEM((ln_modulate_ring_kernel<V>), smem, "vc_ln_modulate");
+      ln_modulate_ring_kernel<V><<<grid_for_ring_rows(rows, V <= 5 ? 5 : 2), ROW_NT, smem, (cudaStream_t)stream>>>(
+          (const __nv_bfloat16*)x, (__nv_bfloat16*)out, (const __nv_bfloat16*)shift_or_beta,
+          (const __nv_bfloat16*)scale_or_gamma, mod_batch_stride, rows, rows_per_batch, D, ldx, ldo, eps, mode);
+      return 0;
+    });
+    VC_CHECK_ARG(rcb == 0, "vc_ln_modulate: unsupported D=%d", D);
+    VC_RETURN_LAUNCH_STATUS("vc_ln_modulate");
+  }
   if (D > 1024) {
     int rcb = dispatch_vpt(D, [&](auto vpt) {
       constexpr int V = decltype(vpt)::value;
@@ -629,6 +845,8 @@ int vc_ln_modulate(const void* x, long long ldx, void* out, long long ldo, const
 int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset, int D,
                        int n_mats, const void* gain_q, const void* gain_k, const void* rope_table, int grid_f,
                        int grid_h, int grid_w, int nf, int nh, int nw, float eps, int apply_rope, void* stream) {
+  const bool force_regs = (apply_rope & 16) != 0;  // VC_ROWS_REGS schedule bit: the register-resident kernel (A/B, tests)
+  apply_rope &= 1;
   VC_CHECK_ARG(n_mats == 1 || n_mats == 2, "vc_rmsnorm_rope_qk: n_mats must be 1 or 2");
   VC_CHECK_ARG(qkv && gain_q && (n_mats == 1 || gain_k), "vc_rmsnorm_rope_qk: null pointer");
   VC_CHECK_ARG(D > 0 && D % 8 == 0 && D <= 8192 && ld % 8 == 0 && ld >= (long long)n_mats * D, "vc_rmsnorm_rope_qk: bad D/ld");
@@ -637,6 +855,22 @@ int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_p
                "vc_rmsnorm_rope_qk: bad rope table split");
   VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && pos_offset >= 0, "vc_rmsnorm_rope_qk: bad rows");
   if (rows == 0) return 0;
+  static const bool use_ring = []() { const char* e = getenv("VC_ROW_KERNELS"); return !(e && !strcmp(e, "regs")); }();
+  if (D > 1024 && use_ring && !force_regs && (!apply_rope || (ROW_NT * 8) % (2 * (nf + nh + nw)) == 0) &&
+      reinterpret_cast<uintptr_t>(qkv) % 16 == 0) {
+    int rcb = dispatch_vpt(D, [&](auto vpt) {
+      constexpr int V = decltype(vpt)::value;
+      const int smem = RING * D * 2;
+      VC_ENSURE_DYN_SMEM((rmsnorm_rope_ring_kernel<V>), smem, "vc_rmsnorm_rope_qk");
+      rmsnorm_rope_ring_kernel<V><<<grid_for_ring_rows(rows, V <= 5 ? 5 : 4), ROW_NT, smem, (cudaStream_t)stream>>>(
+          (__nv_bfloat16*)qkv, ld, rows, rows_per_batch, pos_offset, D, (const __nv_bfloat16*)gain_q,
+          (const __nv_bfloat16*)gain_k, (const float2*)rope_table, grid_f, grid_h, grid_w, nf, nh, nw, eps, apply_rope,
+          n_mats);
+      return 0;
+    });
+    VC_CHECK_ARG(rcb == 0, "vc_rmsnorm_rope_qk: unsupported D=%d", D);
+    VC_RETURN_LAUNCH_STATUS("vc_rmsnorm_rope_qk");
+  }
   if (D > 1024 && (!apply_rope || (ROW_NT * 8) % (2 * (nf + nh + nw)) == 0)) {
     int rcb = dispatch_vpt(D, [&](auto vpt) {
       constexpr int V = decltype(vpt)::value;
