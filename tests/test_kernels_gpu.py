@@ -419,3 +419,31 @@ def test_modulation_table_is_the_bf16_add(ops):
     out2 = torch.zeros_like(out)
     ops.modulation_table(ptrs, n, e0, out2)          # without the head table
     assert torch.equal(out2, out)
+
+
+@pytest.mark.parametrize("rows,D,rpb", [(7, 1536, 4), (1950, 1536, 975), (5000, 5120, 2500), (3, 5120, 2), (4100, 8192, 4100),
+                                        (2221, 2048, 1111), (900, 3072, 450)])
+def test_row_ring_kernels_bit_identical_to_register_kernels(ops, rows, D, rpb):
+    """The asynchronous row-ring kernels (cp.async.bulk prefetch, round 2) and the register-resident kernels (round 1) run
+    the same arithmetic: LayerNorm+modulate, LayerNorm affine and RMSNorm(+RoPE) agree bit for bit — fewer rows than
+    CTAs, many rows per CTA, row-strided inputs."""
+    wide = _rand((rows, D + 64), 90)
+    x = wide[:, :D]                                       # row stride D + 64
+    m = _rand((2, 6, D), 91, 0.1)
+    a = ops.ln_modulate(x, m[:, 0], m[:, 1], rpb)
+    b = ops.ln_modulate(x, m[:, 0], m[:, 1], rpb, regs=True)
+    assert torch.equal(a, b)
+    want = restate.layer_norm(x[:rpb]) * (1 + m[0, 1]) + m[0, 0]
+    assert relerr(a[:rpb], want) < 4e-3
+    g, bt = _rand((D,), 92, 0.5), _rand((D,), 93, 0.1)
+    assert torch.equal(ops.ln_affine(x, g, bt), ops.ln_affine(x, g, bt, regs=True))
+    H = D // 128
+    grid = (2, 5, (rpb + 9) // 10)
+    rope = ops.rope_table(128, grid, "cuda")
+    for n_mats, use_rope in ((2, True), (1, False)):
+        q1 = _rand((rows, 3 * D), 94)
+        q2 = q1.clone()
+        kw = dict(rope=rope, grid=grid) if use_rope else {}
+        ops.rmsnorm_rope_(q1, D, n_mats, g, bt, rpb, pos_offset=3, **kw)
+        ops.rmsnorm_rope_(q2, D, n_mats, g, bt, rpb, pos_offset=3, regs=True, **kw)
+        assert torch.equal(q1, q2), (n_mats, use_rope)

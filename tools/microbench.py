@@ -67,6 +67,36 @@ def bench_rows(B=2, L=32760, D=5120):
               frac_hbm=bytes_ / avg / 1e6 / PEAKS["hbm_gbs"]))
 
 
+def bench_rows_ab(B=2, L=32760, D=5120, rounds=4):
+    """Row kernels at the c3 launch shape: asynchronous row ring (round 2) vs register-resident (round 1), interleaved."""
+    x = torch.randn(B, L, D, device="cuda", dtype=torch.bfloat16)
+    m = torch.randn(B, 6, D, device="cuda", dtype=torch.bfloat16) * 0.1
+    out = torch.empty_like(x)
+    gam = torch.randn(D, device="cuda", dtype=torch.bfloat16)
+    qkv = torch.randn(B * L, 3 * D, device="cuda", dtype=torch.bfloat16)
+    g = torch.ones(D, device="cuda", dtype=torch.bfloat16)
+    grid = (21, 30, 52) if L == 32760 else (1, 1, L)
+    rope = ops.rope_table(128, grid, "cuda")
+    qc = torch.randn(B * L, D, device="cuda", dtype=torch.bfloat16)
+    cases = {
+        "ln_modulate": (lambda r: ops.ln_modulate(x, m[:, 0], m[:, 1], L, out=out, regs=r), 4.0 * B * L * D),
+        "ln_affine": (lambda r: ops.ln_affine(x, gam, gam, out=out, regs=r), 4.0 * B * L * D),
+        "rmsnorm_rope_qk": (lambda r: ops.rmsnorm_rope_(qkv, D, 2, g, g, L, rope=rope, grid=grid, regs=r), 8.0 * B * L * D),
+        "rmsnorm_q_cross": (lambda r: ops.rmsnorm_rope_(qc, D, 1, g, None, L, regs=r), 4.0 * B * L * D),
+    }
+    for name, (fn, bytes_) in cases.items():
+        t = {"ring": [], "regs": []}
+        for _ in range(rounds):
+            for key, r in (("ring", False), ("regs", True)):
+                avg, _ = timeit(lambda: fn(r), iters=10, warmup=2)
+                t[key].append(avg)
+        rec = dict(kernel=name + "_ab", shape=[B, L, D])
+        for key, ts in t.items():
+            ms = sum(ts) / len(ts)
+            rec[key] = dict(ms=ms, gbs=bytes_ / ms / 1e6, frac_hbm=bytes_ / ms / 1e6 / PEAKS["hbm_gbs"])
+        emit(rec)
+
+
 def bench_gemm(M, N, K, epi="bias"):
     a = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
     w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16) / math.sqrt(K)
@@ -203,6 +233,9 @@ if __name__ == "__main__":
         for (N, K, epi) in [(15360, 5120, "bias"), (5120, 5120, "gate_res"), (13824, 5120, "gelu"), (5120, 13824, "gate_res"),
                             (5120, 512, "bias"), (4608, 1536, "bias")]:
             bench_gemm(M, N, K, epi)
+    if "rows_ab" in which:
+        bench_rows_ab()
+        bench_rows_ab(D=1536)
     if "gemm_sched" in which:
         for (M, N, K, epi) in [(65520, 15360, 5120, "bias"), (65520, 5120, 5120, "gate_res"), (65520, 13824, 5120, "gelu"),
                                (65520, 5120, 13824, "gate_res"), (65520, 4608, 1536, "bias"), (65520, 8960, 1536, "gelu"),
