@@ -25,8 +25,9 @@ const char* vc_last_error(void); /* thread-local message of the last non-zero re
  *         wan_transformer3d.py:326-346 with :591-592, :603-604; Head :641-643)
  * mode 1: out[r,:] = LN(x[r,:]) * gamma + beta   (norm3 affine, wan_transformer3d.py:548-550 used at :600);
  *         pass beta as shift_or_beta and gamma as scale_or_gamma.
- * D % 8 == 0, D <= 8192; ldx/ldo = row strides.  Schedule bit (same arithmetic, bit-identical results): mode | 16 selects the
- * register-resident kernel of round 1 instead of the asynchronous row ring (cp.async.bulk prefetch) used for D > 1024. */
+ * D % 8 == 0, D <= 8192; ldx/ldo = row strides.  Schedule bits (same arithmetic, bit-identical results): mode | 16 forces
+ * the register-resident kernel, mode | 32 the asynchronous row ring (cp.async.bulk prefetch, D > 1024); default: the ring for
+ * rows of >= 4 KB (D >= 2048), registers below. */
 int vc_ln_modulate(const void* x, long long ldx, void* out, long long ldo, const void* shift_or_beta,
                    const void* scale_or_gamma, long long mod_batch_stride, long long rows, long long rows_per_batch,
                    int D, float eps, int mode, void* stream);
@@ -39,7 +40,7 @@ int vc_ln_modulate(const void* x, long long ldx, void* out, long long ldo, const
  * Token position = pos_offset + (row % rows_per_batch)  (pos_offset = first token of this rank under sequence
  * parallelism); positions >= grid_f*grid_h*grid_w are normalised but not rotated.  apply_rope = 0: RMSNorm only
  * (cross-attention: q rows with n_mats = 1, :420; text-context [k | v] rows with n_mats = 1, :421).
- * apply_rope | 16: schedule bit as in vc_ln_modulate (register-resident kernel instead of the row ring). */
+ * apply_rope | 16 / | 32: schedule bits as in vc_ln_modulate (default here: the register-resident kernel). */
 int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset, int D,
                        int n_mats, const void* gain_q, const void* gain_k, const void* rope_table, int grid_f,
                        int grid_h, int grid_w, int nf, int nh, int nw, float eps, int apply_rope, void* stream);

@@ -430,13 +430,14 @@ def test_row_ring_kernels_bit_identical_to_register_kernels(ops, rows, D, rpb):
     wide = _rand((rows, D + 64), 90)
     x = wide[:, :D]                                       # row stride D + 64
     m = _rand((2, 6, D), 91, 0.1)
-    a = ops.ln_modulate(x, m[:, 0], m[:, 1], rpb)
+    a = ops.ln_modulate(x, m[:, 0], m[:, 1], rpb, ring=True)
     b = ops.ln_modulate(x, m[:, 0], m[:, 1], rpb, regs=True)
     assert torch.equal(a, b)
     want = restate.layer_norm(x[:rpb]) * (1 + m[0, 1]) + m[0, 0]
     assert relerr(a[:rpb], want) < 4e-3
     g, bt = _rand((D,), 92, 0.5), _rand((D,), 93, 0.1)
-    assert torch.equal(ops.ln_affine(x, g, bt), ops.ln_affine(x, g, bt, regs=True))
+    assert torch.equal(ops.ln_affine(x, g, bt, ring=True), ops.ln_affine(x, g, bt, regs=True))
+    assert torch.equal(ops.ln_affine(x, g, bt), ops.ln_affine(x, g, bt, regs=True))      # whatever the default picks
     H = D // 128
     grid = (2, 5, (rpb + 9) // 10)
     rope = ops.rope_table(128, grid, "cuda")
@@ -444,6 +445,6 @@ def test_row_ring_kernels_bit_identical_to_register_kernels(ops, rows, D, rpb):
         q1 = _rand((rows, 3 * D), 94)
         q2 = q1.clone()
         kw = dict(rope=rope, grid=grid) if use_rope else {}
-        ops.rmsnorm_rope_(q1, D, n_mats, g, bt, rpb, pos_offset=3, **kw)
+        ops.rmsnorm_rope_(q1, D, n_mats, g, bt, rpb, pos_offset=3, ring=True, **kw)
         ops.rmsnorm_rope_(q2, D, n_mats, g, bt, rpb, pos_offset=3, regs=True, **kw)
         assert torch.equal(q1, q2), (n_mats, use_rope)

@@ -79,10 +79,10 @@ def bench_rows_ab(B=2, L=32760, D=5120, rounds=4):
     rope = ops.rope_table(128, grid, "cuda")
     qc = torch.randn(B * L, D, device="cuda", dtype=torch.bfloat16)
     cases = {
-        "ln_modulate": (lambda r: ops.ln_modulate(x, m[:, 0], m[:, 1], L, out=out, regs=r), 4.0 * B * L * D),
-        "ln_affine": (lambda r: ops.ln_affine(x, gam, gam, out=out, regs=r), 4.0 * B * L * D),
-        "rmsnorm_rope_qk": (lambda r: ops.rmsnorm_rope_(qkv, D, 2, g, g, L, rope=rope, grid=grid, regs=r), 8.0 * B * L * D),
-        "rmsnorm_q_cross": (lambda r: ops.rmsnorm_rope_(qc, D, 1, g, None, L, regs=r), 4.0 * B * L * D),
+        "ln_modulate": (lambda r: ops.ln_modulate(x, m[:, 0], m[:, 1], L, out=out, regs=r, ring=not r), 4.0 * B * L * D),
+        "ln_affine": (lambda r: ops.ln_affine(x, gam, gam, out=out, regs=r, ring=not r), 4.0 * B * L * D),
+        "rmsnorm_rope_qk": (lambda r: ops.rmsnorm_rope_(qkv, D, 2, g, g, L, rope=rope, grid=grid, regs=r, ring=not r), 8.0 * B * L * D),
+        "rmsnorm_q_cross": (lambda r: ops.rmsnorm_rope_(qc, D, 1, g, None, L, regs=r, ring=not r), 4.0 * B * L * D),
     }
     for name, (fn, bytes_) in cases.items():
         t = {"ring": [], "regs": []}

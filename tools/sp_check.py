@@ -24,25 +24,34 @@ def main():
     ctx = [torch.randn(n, 256, generator=g, device="cuda").bfloat16() * 0.1 for n in (37, 512)]
     t = torch.full((2,), 500.0, device="cuda")
     L = grid[0] * grid[1] * grid[2] // 4
-    y1 = model(x, t, geo, ctx, L).float()
+    # second case: a token count that does NOT divide by the world size (and seq_len > L): the zero-padded tail tokens
+    # must not be attended (k_lens), exactly as on one GPU
+    grid_b = (3, 14, 26)   # L = 3*7*13 = 273
+    xb = torch.randn(2, 16, *grid_b, generator=g, device="cuda").bfloat16()
+    geob = torch.randn(2, 128, *grid_b, generator=g, device="cuda").bfloat16()
+    Lb = 273 + 5
+    cases = [("divisible", (x, t, geo, ctx, L)), ("ragged+padded", (xb, t, geob, ctx, Lb))]
+    singles = [model(*a).float() for _, a in cases]
     model.enable_multi_gpus_inference()
     all_ok = True
     for mode in ("nccl", "fused"):  # NCCL all_to_all path, then the peer-memory path fused into the kernels
         os.environ["VC_SP_MODE"] = mode
         model._px, model._px_failed = None, False
-        yp = model(x, t, geo, ctx, L).float()
-        yp2 = model(x, t, geo, ctx, L).float()  # second call: buffers are reused across steps
-        torch.cuda.synchronize()
-        used = "fused" if model._px is not None else "nccl"
-        cos = float(torch.nn.functional.cosine_similarity(y1.flatten().double(), yp.flatten().double(), dim=0))
-        rel = float((y1 - yp).norm() / y1.norm())
-        ok = cos > 0.9999 and rel < 1e-2 and torch.equal(yp, yp2) and used == mode
-        flags = torch.tensor([1.0 if ok else 0.0], device="cuda")
-        dist.all_reduce(flags, op=dist.ReduceOp.MIN)
-        all_ok = all_ok and flags.item() == 1
-        if rank == 0:
-            print(f"sp_check world={world} mode={mode} (ran {used}): cosine {cos:.7f} rel-L2 {rel:.5f} "
-                  f"repeatable={torch.equal(yp, yp2)} -> {'OK' if flags.item() == 1 else 'FAIL'}", flush=True)
+        for (name, a), y1 in zip(cases, singles):
+            yp = model(*a).float()
+            yp2 = model(*a).float()  # second call: buffers are reused across steps
+            torch.cuda.synchronize()
+            used = "fused" if model._px is not None else "nccl"
+            cos = float(torch.nn.functional.cosine_similarity(y1.flatten().double(), yp.flatten().double(), dim=0))
+            rel = float((y1 - yp).norm() / y1.norm())
+            ok = cos > 0.9999 and rel < 1e-2 and torch.equal(yp, yp2) and used == mode
+            flags = torch.tensor([1.0 if ok else 0.0], device="cuda")
+            dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+            all_ok = all_ok and flags.item() == 1
+            if rank == 0:
+                print(f"sp_check world={world} mode={mode} (ran {used}) case={name}: cosine {cos:.7f} rel-L2 {rel:.5f} "
+                      f"bit-identical-to-1gpu={torch.equal(yp, y1)} repeatable={torch.equal(yp, yp2)} -> "
+                      f"{'OK' if flags.item() == 1 else 'FAIL'}", flush=True)
     dist.destroy_process_group()
     sys.exit(0 if all_ok else 1)
 

@@ -801,12 +801,20 @@ int vc_ln_modulate(const void* x, long long ldx, void* out, long long ldo, const
   VC_CHECK_ARG(x && out && shift_or_beta && scale_or_gamma, "vc_ln_modulate: null pointer");
   VC_CHECK_ARG(D > 0 && D % 8 == 0 && D <= 8192, "vc_ln_modulate: D=%d must be a multiple of 8 and <= 8192", D);
   VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && ldx % 8 == 0 && ldo % 8 == 0, "vc_ln_modulate: bad rows/strides");
-  const bool force_regs = (mode & 16) != 0;  // VC_ROWS_REGS schedule bit: the register-resident kernel (A/B, tests)
-  mode &= ~16;
+  const bool force_regs = (mode & 16) != 0;  // schedule bits (A/B, tests): 16 = register-resident kernel, 32 = row ring
+  const bool force_ring = (mode & 32) != 0;
+  mode &= ~48;
   VC_CHECK_ARG(mode == 0 || mode == 1, "vc_ln_modulate: mode must be 0 (modulate) or 1 (affine)");
   if (rows == 0) return 0;
-  // VC_ROW_KERNELS = ring (default: asynchronous row ring, cp.async.bulk) | regs (round-1 register-resident kernels)
-  static const bool use_ring = []() { const char* e = getenv("VC_ROW_KERNELS"); return !(e && !strcmp(e, "regs")); }();
+  // Row ring (cp.async.bulk prefetch) for rows of >= 4 KB, register-resident kernel below that.  Measured on B200 at the c3
+  // shape (profiles/rows_ab_r02.jsonl; in the step: profiles/bench_c3_r02c_{ring,regs}.json): LN+modulate 5.29 TB/s in the
+  // step with the ring vs 4.04 with registers (alone 5.32 vs 5.04), norm3 affine 4.67 vs 3.84; at D = 1536 (3 KB rows) the
+  // ring loses (3.95 vs 4.26 TB/s alone).  VC_ROW_KERNELS = ring | regs overrides; mode | 16 forces registers per call.
+  static const int ring_env = []() {
+    const char* e = getenv("VC_ROW_KERNELS");
+    return !e ? -1 : !strcmp(e, "regs") ? 0 : !strcmp(e, "ring") ? 1 : -1;
+  }();
+  const bool use_ring = force_ring || (ring_env >= 0 ? ring_env == 1 : D >= 2048);
   if (D > 1024 && use_ring && !force_regs && reinterpret_cast<uintptr_t>(x) % 16 == 0) {
     int rcb = dispatch_vpt(D, [&](auto vpt) {
       constexpr int V = decltype(vpt)::value;
@@ -845,7 +853,8 @@ int vc_ln_modulate(const void* x, long long ldx, void* out, long long ldo, const
 int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset, int D,
                        int n_mats, const void* gain_q, const void* gain_k, const void* rope_table, int grid_f,
                        int grid_h, int grid_w, int nf, int nh, int nw, float eps, int apply_rope, void* stream) {
-  const bool force_regs = (apply_rope & 16) != 0;  // VC_ROWS_REGS schedule bit: the register-resident kernel (A/B, tests)
+  const bool force_regs = (apply_rope & 16) != 0;  // schedule bits as in vc_ln_modulate: 16 = registers, 32 = row ring
+  const bool force_ring = (apply_rope & 32) != 0;
   apply_rope &= 1;
   VC_CHECK_ARG(n_mats == 1 || n_mats == 2, "vc_rmsnorm_rope_qk: n_mats must be 1 or 2");
   VC_CHECK_ARG(qkv && gain_q && (n_mats == 1 || gain_k), "vc_rmsnorm_rope_qk: null pointer");
@@ -855,7 +864,11 @@ int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_p
                "vc_rmsnorm_rope_qk: bad rope table split");
   VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && pos_offset >= 0, "vc_rmsnorm_rope_qk: bad rows");
   if (rows == 0) return 0;
-  static const bool use_ring = []() { const char* e = getenv("VC_ROW_KERNELS"); return !(e && !strcmp(e, "regs")); }();
+  // The in-place RMSNorm(+RoPE) keeps the register-resident kernel (it already prefetches the next segment into registers):
+  // the ring variant is on par alone at D = 5120 (5.80 vs 5.76 TB/s) but slower in the step (4.29 vs 4.77 TB/s) and at
+  // D = 1536; it runs only with VC_ROW_KERNELS=ring (kept for experiments, bit-identical).
+  static const bool ring_env = []() { const char* e = getenv("VC_ROW_KERNELS"); return e && !strcmp(e, "ring"); }();
+  const bool use_ring = ring_env || force_ring;
   if (D > 1024 && use_ring && !force_regs && (!apply_rope || (ROW_NT * 8) % (2 * (nf + nh + nw)) == 0) &&
       reinterpret_cast<uintptr_t>(qkv) % 16 == 0) {
     int rcb = dispatch_vpt(D, [&](auto vpt) {

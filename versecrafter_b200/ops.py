@@ -66,7 +66,7 @@ def _rows2d(t, name):
     return t.numel() // t.shape[-1], t.shape[-1]
 
 
-def ln_modulate(x, shift, scale, rows_per_batch, eps=1e-6, out=None, regs=False):
+def ln_modulate(x, shift, scale, rows_per_batch, eps=1e-6, out=None, regs=False, ring=False):
     """out = LN(x) * (1 + scale[b]) + shift[b];  x [rows, D] (or [B, L, D]); shift/scale [B, D] views (bf16)."""
     global launch_count
     rows, ldx = _rows2d(x, "x")
@@ -81,12 +81,12 @@ def ln_modulate(x, shift, scale, rows_per_batch, eps=1e-6, out=None, regs=False)
     lib = _lib.load()
     with _timed("ln_modulate", 4.0 * rows * D):
         _lib.check(lib.vc_ln_modulate(_ptr(x), ldx, _ptr(out), ldo, _ptr(sh2), _ptr(sc2), sh2.stride(0), rows,
-                                      rows_per_batch, D, eps, 16 if regs else 0, _stream()), "vc_ln_modulate")
+                                      rows_per_batch, D, eps, (16 if regs else 0) | (32 if ring else 0), _stream()), "vc_ln_modulate")
     launch_count += 1
     return out
 
 
-def ln_affine(x, gamma, beta, eps=1e-6, out=None, regs=False):
+def ln_affine(x, gamma, beta, eps=1e-6, out=None, regs=False, ring=False):
     """out = LN(x) * gamma + beta (norm3)."""
     global launch_count
     rows, ldx = _rows2d(x, "x")
@@ -98,7 +98,7 @@ def ln_affine(x, gamma, beta, eps=1e-6, out=None, regs=False):
     lib = _lib.load()
     with _timed("ln_affine", 4.0 * rows * D):
         _lib.check(lib.vc_ln_modulate(_ptr(x), ldx, _ptr(out), ldo, _ptr(beta), _ptr(gamma), 0, rows, max(rows, 1), D, eps,
-                                      17 if regs else 1, _stream()), "vc_ln_modulate")
+                                      1 | (16 if regs else 0) | (32 if ring else 0), _stream()), "vc_ln_modulate")
     launch_count += 1
     return out
 
@@ -119,7 +119,7 @@ def rope_table(head_dim, grid, device, theta=10000.0):
     return torch.cat(parts).to(torch.float32).to(device).contiguous(), (nf, nh, nw)
 
 
-def rmsnorm_rope_(buf, D, n_mats, gain_q, gain_k, rows_per_batch, eps=1e-6, rope=None, grid=None, pos_offset=0, regs=False):
+def rmsnorm_rope_(buf, D, n_mats, gain_q, gain_k, rows_per_batch, eps=1e-6, rope=None, grid=None, pos_offset=0, regs=False, ring=False):
     """In place: first n_mats D-wide column blocks of buf [rows, ld] <- RoPE(RMSNorm(.) * gain).
     rope = (table, (nf, nh, nw)) from rope_table, grid = (F, H', W'); rope=None -> RMSNorm only."""
     global launch_count
@@ -140,7 +140,7 @@ def rmsnorm_rope_(buf, D, n_mats, gain_q, gain_k, rows_per_batch, eps=1e-6, rope
         tptr, do = ctypes.c_void_p(0), 0
     with _timed("rmsnorm_rope", 4.0 * rows * D * n_mats):
         _lib.check(lib.vc_rmsnorm_rope_qk(_ptr(buf), ld, rows, rows_per_batch, pos_offset, D, n_mats, _ptr(gain_q),
-                                          _ptr(gain_k), tptr, gf, gh, gw, nf, nh, nw, eps, do | (16 if regs else 0), _stream()),
+                                          _ptr(gain_k), tptr, gf, gh, gw, nf, nh, nw, eps, do | (16 if regs else 0) | (32 if ring else 0), _stream()),
                    "vc_rmsnorm_rope_qk")
     launch_count += 1
     return buf
