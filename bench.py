@@ -244,6 +244,8 @@ def summarize_timing(timing, peaks):
         if name in ("gemm", "attn_self", "attn_cross", "patch_embed"):
             ent["tflops"] = work / tot / 1e9
             ent["frac_of_bf16_sustained"] = ent["tflops"] / peaks["bf16_tflops_sustained"]
+        elif name == "barrier":   # cross-GPU stream barriers (N > 1): time on THIS rank = barrier cost + waiting for the peers
+            pass
         else:
             ent["gbs"] = work / tot / 1e6
             ent["frac_of_hbm"] = ent["gbs"] / peaks["hbm_gbs"]

@@ -113,7 +113,15 @@ int vc_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, int 
  * vc_rmsnorm_rope_qkv_scatter: rows [q(D) | k(D) | v(D)] (row stride ld) of THIS rank's tokens -> q,k normalised and
  *   rotated exactly as vc_rmsnorm_rope_qk, v copied, and head h of global token t of sample b stored at
  *   peer_recv[h / heads_per_peer] + ((((which*n_batch + b)*l_total + t)*heads_per_peer + h % heads_per_peer)*head_dim,
- *   which = 0,1,2 for q,k,v; n_batch = rows / rows_per_batch; t = pos_offset + row % rows_per_batch.
+ *   which = 0,1,2 for q,k,v; n_batch = rows / rows_per_batch; t = pos_offset + row % rows_per_batch.  which_mask
+ *   (bit 0 q, bit 1 k, bit 2 v; 7 = all) selects the matrices of this launch, so the caller can scatter q while the
+ *   k GEMM still runs (versecrafter_b200/sp.py); bit 3 (8): stores issued by the TMA engine (one cp.async.bulk per row,
+ *   matrix and peer) instead of per-thread 16-byte stores; bits 8-15: cap on resident CTAs per SM (0 = default).
+ * vc_gemm_bf16_scatter: Y = A . W^T + bias (as vc_gemm_bf16 with VC_EPI_BIAS) whose epilogue stores head h of token row
+ *   r at peer_recv[h / heads_per_peer] + (((b*l_total + t)*heads_per_peer + h % heads_per_peer)*head_dim, b = r /
+ *   rows_per_batch, t = pos_offset + r % rows_per_batch: the v Linear (wan_transformer3d.py:383-389) and its Ulysses
+ *   all-to-all in one kernel.  peer_recv[i] points at the matrix' own block of peer i's buffer; head_dim = 128;
+ *   sched = 0 or one VC_GEMM_SCHED_* bit.
  * vc_flash_attn_fwd_scatter: vc_flash_attn_fwd on the local heads over all tokens, with query row t stored at row
  *   t % rows_per_peer of peer_o[t / rows_per_peer] (strides o_strides; the caller bakes its head offset into the
  *   pointers).  variant >= 2. */
@@ -121,7 +129,18 @@ int vc_rmsnorm_rope_qkv_scatter(const void* qkv, long long ld, long long rows, l
                                 long long pos_offset, int D, const void* gain_q, const void* gain_k,
                                 const void* rope_table, int grid_f, int grid_h, int grid_w, int nf, int nh, int nw,
                                 float eps, void* const* peer_recv, int n_peers, int heads_per_peer, long long l_total,
-                                void* stream);
+                                int which_mask, void* stream);
+/* Stream-ordered barrier of the sequence-parallel group over peer-mapped flag arrays (one u32 per peer, zero-initialised):
+ * publishes `epoch` (1-based call count, equal on all ranks) into slot [rank] of every peer's array and waits until every
+ * peer's epoch has arrived in this rank's array.  Work enqueued after it starts only after the peers' kernels enqueued
+ * before their matching call have completed.  A peer that does not arrive within timeout_ms (0 = 5000) sets
+ * *status = 0x80000000 | peer instead of hanging the GPU. */
+int vc_peer_barrier(void* const* flags, int rank, int n_peers, unsigned int epoch, int timeout_ms, void* status,
+                    void* stream);
+int vc_gemm_bf16_scatter(const void* A, long long lda, const void* W, long long ldw, long long M, long long N,
+                         long long K, const void* bias, long long rows_per_batch, long long pos_offset,
+                         void* const* peer_recv, int n_peers, int heads_per_peer, int head_dim, long long l_total,
+                         int sched, void* stream);
 int vc_flash_attn_fwd_scatter(const void* q, const void* k, const void* v, int B, int H, int Lq, int Lk, int head_dim,
                               const long long* q_strides, const long long* k_strides, const long long* v_strides,
                               void* const* peer_o, int n_peers, int rows_per_peer, const long long* o_strides,

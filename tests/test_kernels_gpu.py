@@ -321,6 +321,52 @@ def test_ulysses_fused_kernels_emulated_ranks(ops, P, H, grid):
         assert torch.equal(attn[r], o_cut[:, r * Lp:(r + 1) * Lp]), r
 
 
+@pytest.mark.parametrize("P,H,grid,K", [(2, 4, (2, 8, 24), 256), (8, 40, (3, 13, 40), 512), (4, 8, (5, 6, 12), 320)])
+def test_ulysses_overlapped_pieces_emulated_ranks(ops, P, H, grid, K):
+    """The pieces of sp.ulysses_qkv_attention_overlapped with the ranks emulated on one GPU: q and k scattered by separate
+    masked launches of the RMSNorm+RoPE scatter kernel, v = Linear(h) scattered by the GEMM's own epilogue
+    (vc_gemm_bf16_scatter, every schedule) — bit-identical to the one-launch scatter of the fused QKV GEMM's output."""
+    B, d = 2, 128
+    D, L = H * d, grid[0] * grid[1] * grid[2]
+    Lp, Hp = L // P, H // P
+    h = _rand((B, L, K), 60)
+    w = _rand((3 * D, K), 61, 1 / math.sqrt(K))
+    bias = _rand((3 * D,), 62)
+    gq = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    gk = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16)
+    rope = ops.rope_table(d, grid, "cuda")
+    want = [torch.full((3, B, L, Hp, d), float("nan"), device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    for r in range(P):   # the one-kernel path: fused QKV GEMM, then one scatter launch
+        qkv = ops.gemm(h[:, r * Lp:(r + 1) * Lp].reshape(B * Lp, K).contiguous(), w, bias)
+        ops.rmsnorm_rope_qkv_scatter(qkv, D, gq, gk, Lp, [t.data_ptr() for t in want], Hp, L, rope, grid, pos_offset=r * Lp)
+    for sched, bulk, cap in ((0, False, 0), (ops.SCHED_SINGLE, True, 0), (ops.SCHED_PAIR, True, 1), (ops.SCHED_MULTICAST, False, 2)):
+        got = [torch.full((3, B, L, Hp, d), float("nan"), device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+        ptrs = [t.data_ptr() for t in got]
+        v_block = 2 * B * L * Hp * d * 2
+        for r in range(P):
+            hr = h[:, r * Lp:(r + 1) * Lp].reshape(B * Lp, K).contiguous()
+            qkv = torch.full((B * Lp, 3 * D), float("nan"), device="cuda", dtype=torch.bfloat16)
+            ops.gemm(hr, w[:D], bias[:D], out=qkv[:, :D])
+            ops.rmsnorm_rope_qkv_scatter(qkv, D, gq, gk, Lp, ptrs, Hp, L, rope, grid, pos_offset=r * Lp, which_mask=1, bulk=bulk,
+                                         cta_cap=cap)
+            ops.gemm(hr, w[D:2 * D], bias[D:2 * D], out=qkv[:, D:2 * D])
+            ops.rmsnorm_rope_qkv_scatter(qkv, D, gq, gk, Lp, ptrs, Hp, L, rope, grid, pos_offset=r * Lp, which_mask=2, bulk=bulk,
+                                         cta_cap=cap)
+            ops.gemm_scatter(hr, w[2 * D:], bias[2 * D:], Lp, [p_ + v_block for p_ in ptrs], Hp, L, pos_offset=r * Lp,
+                             sched=sched)
+            assert torch.isnan(qkv[:, 2 * D:].float()).all()     # v never exists as a local matrix
+        for p_ in range(P):
+            for i in range(3):
+                assert torch.equal(got[p_][i], want[p_][i]), (sched, p_, i)
+    # the one-launch scatter (all three matrices) with bulk stores
+    got = [torch.full((3, B, L, Hp, d), float("nan"), device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    for r in range(P):
+        qkv = ops.gemm(h[:, r * Lp:(r + 1) * Lp].reshape(B * Lp, K).contiguous(), w, bias)
+        ops.rmsnorm_rope_qkv_scatter(qkv, D, gq, gk, Lp, [t.data_ptr() for t in got], Hp, L, rope, grid, pos_offset=r * Lp, bulk=True)
+    for p_ in range(P):
+        assert torch.equal(got[p_], want[p_]), p_
+
+
 def test_gemm_rejects_output_over_its_own_input(ops):
     """The persistent kernel re-reads A rows after C tiles of those rows are stored: A aliasing C is an argument error
     (before_proj wrote over its input); disjoint column blocks of one buffer are allowed."""

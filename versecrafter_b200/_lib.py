@@ -24,7 +24,10 @@ SIGNATURES = {
     "vc_gemm_bf16": (_i, [_vp, _c_ll, _vp, _c_ll, _vp, _c_ll, _c_ll, _c_ll, _c_ll, _i, _vp, _vp, _c_ll, _c_ll, _vp, _c_ll, _f, _vp]),
     "vc_flash_attn_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _llp, _llp, _llp, _llp, _f, _i, _vp]),
     "vc_rmsnorm_rope_qkv_scatter": (_i, [_vp, _c_ll, _c_ll, _c_ll, _c_ll, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f,
-                                         _vpp, _i, _i, _c_ll, _vp]),
+                                         _vpp, _i, _i, _c_ll, _i, _vp]),
+    "vc_peer_barrier": (_i, [_vpp, _i, _i, ctypes.c_uint, _i, _vp, _vp]),
+    "vc_gemm_bf16_scatter": (_i, [_vp, _c_ll, _vp, _c_ll, _c_ll, _c_ll, _c_ll, _vp, _c_ll, _c_ll, _vpp, _i, _i, _i, _c_ll, _i,
+                                  _vp]),
     "vc_flash_attn_fwd_scatter": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _llp, _llp, _llp, _vpp, _i, _i, _llp, _f, _i,
                                        _vp]),
     "vc_patch_embed_supported": (_i, [_i, _i, _i, _i, _i]),

@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libvc_b200.so")
-SOURCES = ["api.cu", "embed_kernels.cu", "norm_kernels.cu", "gemm_tcgen05.cu", "patch_embed_tcgen05.cu", "loop_glue.cu", "control_maps.cu", "raster.cu", "flash_attn_tcgen05.cu"]
+SOURCES = ["api.cu", "embed_kernels.cu", "norm_kernels.cu", "gemm_tcgen05.cu", "patch_embed_tcgen05.cu", "loop_glue.cu", "control_maps.cu", "raster.cu", "peer_sync.cu", "flash_attn_tcgen05.cu"]
 # sources whose fp32 divisions / exp must be IEEE / libm-accurate (bit parity with the reference's torch arithmetic)
 PRECISE_SOURCES = {"control_maps.cu", "raster.cu", "embed_kernels.cu"}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "--use_fast_math",

@@ -27,8 +27,9 @@ constexpr int EPI_WARPS = 8;
 constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;  // TMA warp, MMA warp, epilogue warps
 constexpr int DEFAULT_SCHED = 0;  // see vc_gemm_bf16: 0 single, 1 multicast cluster, 2 CTA pair
 
-enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16, SCHED_MULTICAST = 64, SCHED_PAIR = 128,
-             SCHED_SINGLE = 256 };
+enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16, EPI_SCATTER = 32, SCHED_MULTICAST = 64,
+             SCHED_PAIR = 128, SCHED_SINGLE = 256 };
+constexpr int SCATTER_HEAD_DIM = 128;  // EPI_SCATTER: a head is 128 columns (256 bytes), so a 32-column chunk has one head
 
 struct GemmParams {
   long long M, N, K;
@@ -44,6 +45,10 @@ struct GemmParams {
   int m_tiles, n_tiles;
   int group_m;  // M tiles per rasterisation group (see vc_gemm_bf16)
   int l2_hint;  // bit 0: A loads evict_last; bit 1: W loads evict_first; bit 2: streaming C stores
+  // EPI_SCATTER (vc_gemm_bf16_scatter): C is not one matrix but the head-scattered receive buffers of the peer GPUs
+  __nv_bfloat16* peer[8];   // base of this matrix' block ([n_batch, l_total, heads_per_peer, 128]) in every peer's buffer
+  int heads_per_peer;
+  long long l_total, pos_offset;
 };
 
 __device__ __forceinline__ void tile_coords(int t, int m_tiles, int n_tiles, int group_m, int& m, int& n) {
@@ -71,8 +76,17 @@ __device__ __forceinline__ float gelu_tanh(float x) {
 // longer than its 24 k-blocks of MMAs and the kernel fell to 0.71 of the bf16 peak, below cuBLASLt.)
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32_t* r, long long col0, bool row_ok,
-                                               __nv_bfloat16* crow, const __nv_bfloat16* rrow, const __nv_bfloat16* grow) {
+                                               __nv_bfloat16* crow, const __nv_bfloat16* rrow, const __nv_bfloat16* grow,
+                                               long long srow) {
   if (row_ok && col0 < p.N) {
+    if (EPI & EPI_SCATTER) {
+      // head-scatter store (Ulysses all-to-all inside the epilogue): columns [col0, col0+32) belong to ONE head; it lives
+      // at the peer that owns the head, row (b, global token) of that peer's [n_batch, l_total, heads_per_peer, 128] block
+      const int head = (int)(col0 / SCATTER_HEAD_DIM);
+      const int peer = head / p.heads_per_peer;
+      const int hl = head - peer * p.heads_per_peer;
+      crow = p.peer[peer] + (srow + hl) * SCATTER_HEAD_DIM - (long long)head * SCATTER_HEAD_DIM;  // + col below
+    }
 #pragma unroll
     for (int g = 0; g < 4; ++g) {  // 8 columns = one 16-byte store
       const long long col = col0 + g * 8;
@@ -138,6 +152,11 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t t_ad
   const __nv_bfloat16* rrow = (EPI & EPI_RES) ? p.residual + row * p.ldr : nullptr;
   const __nv_bfloat16* grow =
       (EPI & EPI_GATE) ? p.gate + (row_ok ? row / p.rows_per_batch : 0) * p.gate_stride : nullptr;
+  long long srow = 0;
+  if (EPI & EPI_SCATTER) {  // (b * l_total + global token) * heads_per_peer: the row of local head 0 in a peer's block
+    const long long b = row_ok ? row / p.rows_per_batch : 0;
+    srow = (b * p.l_total + p.pos_offset + (row - b * p.rows_per_batch)) * p.heads_per_peer;
+  }
   constexpr int CHUNKS = BN / 32 / 2;  // per warp
   const int c0 = half * CHUNKS;
   const long long colbase = (long long)n * BN + c0 * 32;
@@ -147,10 +166,10 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t t_ad
   for (int c = 0; c < CHUNKS; c += 2) {
     vc::tmem_ld_wait();
     vc::tmem_ld32(t_addr + (c0 + c + 1) * 32, rb);
-    epilogue_chunk<EPI>(p, ra, colbase + c * 32, row_ok, crow, rrow, grow);
+    epilogue_chunk<EPI>(p, ra, colbase + c * 32, row_ok, crow, rrow, grow, srow);
     vc::tmem_ld_wait();
     if (c + 2 < CHUNKS) vc::tmem_ld32(t_addr + (c0 + c + 2) * 32, ra);
-    epilogue_chunk<EPI>(p, rb, colbase + (c + 1) * 32, row_ok, crow, rrow, grow);
+    epilogue_chunk<EPI>(p, rb, colbase + (c + 1) * 32, row_ok, crow, rrow, grow, srow);
   }
 }
 
@@ -495,10 +514,16 @@ using vc_host::sm_count;
 
 }  // namespace
 
-extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long long ldw, void* C, long long ldc,
-                            long long M, long long N, long long K, int epilogue, const void* bias, const void* gate,
-                            long long gate_batch_stride, long long rows_per_batch, const void* residual,
-                            long long ldr, float scale, void* stream) {
+// `sc` != nullptr: the head-scatter epilogue (vc_gemm_bf16_scatter); its peer / layout fields are copied into the kernel
+// parameters and C is unused.
+static int gemm_entry(const void* A, long long lda, const void* W, long long ldw, void* C, long long ldc,
+                      long long M, long long N, long long K, int epilogue, const void* bias, const void* gate,
+                      long long gate_batch_stride, long long rows_per_batch, const void* residual,
+                      long long ldr, float scale, void* stream, const GemmParams* sc) {
+  if (sc) {  // placeholders that satisfy the dense-C checks below; no thread dereferences C with EPI_SCATTER
+    C = const_cast<void*>(static_cast<const void*>(sc->peer[0]));
+    ldc = N;
+  }
   VC_CHECK_ARG(A && W && C, "vc_gemm_bf16: null operand");
   VC_CHECK_ARG(M >= 0 && N > 0 && K > 0, "vc_gemm_bf16: bad shape M=%lld N=%lld K=%lld", M, N, K);
   VC_CHECK_ARG(N % 8 == 0 && K % 8 == 0, "vc_gemm_bf16: N and K must be multiples of 8 (N=%lld K=%lld)", N, K);
@@ -510,7 +535,7 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   VC_CHECK_ARG(!(epilogue & EPI_GATE) || (gate && rows_per_batch > 0), "vc_gemm_bf16: gate epilogue without gate");
   VC_CHECK_ARG(!(epilogue & EPI_RES) || (residual && ldr % 8 == 0 && ldr >= N), "vc_gemm_bf16: residual epilogue without residual");
   if (M == 0) return 0;
-  {
+  if (!sc) {
     // The kernel is persistent and multi-tile: tile (m, n) stores its C block while other CTAs / later waves still load
     // A[m rows, 0:K] for the other N tiles, so A must not overlap C (only `residual` may alias C: each element is read
     // and written by the same thread).  Interleaved column blocks of one row-strided buffer (same ld, disjoint
@@ -568,6 +593,10 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
   p.rows_per_batch = rows_per_batch > 0 ? rows_per_batch : 1;
   p.residual = (const __nv_bfloat16*)residual; p.ldr = ldr;
   p.scale = scale;
+  for (int i = 0; i < 8; ++i) p.peer[i] = sc ? sc->peer[i] : nullptr;
+  p.heads_per_peer = sc ? sc->heads_per_peer : 1;
+  p.l_total = sc ? sc->l_total : 0;
+  p.pos_offset = sc ? sc->pos_offset : 0;
   p.m_tiles = (int)((M + BM - 1) / BM);
   p.n_tiles = (int)((N + BN - 1) / BN);
   // Rasterisation: tiles are visited group by group, a group = group_m M-tiles x all N-tiles (M fastest), so the A rows of
@@ -606,10 +635,53 @@ extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long lo
     case EPI_BIAS | EPI_RES: rc = launch<EPI_BIAS | EPI_RES>(ta, tb, p, grid, sched, s); break;
     case EPI_BIAS | EPI_GATE | EPI_RES: rc = launch<EPI_BIAS | EPI_GATE | EPI_RES>(ta, tb, p, grid, sched, s); break;
     case EPI_BIAS | EPI_SCALE | EPI_RES: rc = launch<EPI_BIAS | EPI_SCALE | EPI_RES>(ta, tb, p, grid, sched, s); break;
+    case EPI_BIAS | EPI_SCATTER:
+      if (sc) { rc = launch<EPI_BIAS | EPI_SCATTER>(ta, tb, p, grid, sched, s); break; }
+      [[fallthrough]];
     default:
       vc_host::set_error("vc_gemm_bf16: unsupported epilogue mask %d", epilogue);
       return -1;
   }
   if (rc) return rc;
   VC_RETURN_LAUNCH_STATUS("vc_gemm_bf16");
+}
+
+extern "C" int vc_gemm_bf16(const void* A, long long lda, const void* W, long long ldw, void* C, long long ldc,
+                            long long M, long long N, long long K, int epilogue, const void* bias, const void* gate,
+                            long long gate_batch_stride, long long rows_per_batch, const void* residual,
+                            long long ldr, float scale, void* stream) {
+  VC_CHECK_ARG(!(epilogue & EPI_SCATTER), "vc_gemm_bf16: the scatter epilogue is vc_gemm_bf16_scatter");
+  return gemm_entry(A, lda, W, ldw, C, ldc, M, N, K, epilogue, bias, gate, gate_batch_stride, rows_per_batch, residual, ldr,
+                    scale, stream, nullptr);
+}
+
+// Linear + Ulysses all-to-all in one kernel: Y = A . W^T + bias for this rank's token rows, every head's 128 columns
+// stored straight into the receive buffer of the peer GPU that owns the head (same destination formula as
+// vc_rmsnorm_rope_qkv_scatter; `peer_recv[i]` = base of this matrix' [n_batch, l_total, heads_per_peer, 128] block in
+// peer i's buffer).  Used for v, which needs no normalisation: its exchange leaves the critical path and rides under
+// the GEMM's own main loop (wan_transformer3d.py:383-389 `v = self.v(x)` + xfuser's SeqAllToAll4D).
+extern "C" int vc_gemm_bf16_scatter(const void* A, long long lda, const void* W, long long ldw, long long M, long long N,
+                                    long long K, const void* bias, long long rows_per_batch, long long pos_offset,
+                                    void* const* peer_recv, int n_peers, int heads_per_peer, int head_dim,
+                                    long long l_total, int sched, void* stream) {
+  VC_CHECK_ARG(peer_recv && bias, "vc_gemm_bf16_scatter: null pointer");
+  VC_CHECK_ARG(n_peers >= 1 && n_peers <= 8, "vc_gemm_bf16_scatter: n_peers=%d must be in 1..8", n_peers);
+  VC_CHECK_ARG(head_dim == SCATTER_HEAD_DIM, "vc_gemm_bf16_scatter: head_dim=%d must be 128", head_dim);
+  VC_CHECK_ARG(heads_per_peer > 0 && (long long)heads_per_peer * n_peers * head_dim == N,
+               "vc_gemm_bf16_scatter: heads_per_peer * n_peers * head_dim must equal N=%lld", N);
+  VC_CHECK_ARG(M >= 0 && rows_per_batch > 0 && M % rows_per_batch == 0 && pos_offset >= 0 &&
+                   pos_offset + rows_per_batch <= l_total,
+               "vc_gemm_bf16_scatter: bad rows / positions");
+  VC_CHECK_ARG(sched == 0 || sched == SCHED_MULTICAST || sched == SCHED_PAIR || sched == SCHED_SINGLE,
+               "vc_gemm_bf16_scatter: sched must be 0 or one VC_GEMM_SCHED_* bit");
+  GemmParams sc = {};
+  for (int i = 0; i < n_peers; ++i) {
+    VC_CHECK_ARG(peer_recv[i] && (uintptr_t)peer_recv[i] % 16 == 0, "vc_gemm_bf16_scatter: bad peer pointer %d", i);
+    sc.peer[i] = (__nv_bfloat16*)peer_recv[i];
+  }
+  sc.heads_per_peer = heads_per_peer;
+  sc.l_total = l_total;
+  sc.pos_offset = pos_offset;
+  return gemm_entry(A, lda, W, ldw, nullptr, 0, M, N, K, EPI_BIAS | EPI_SCATTER | sched, bias, nullptr, 0, rows_per_batch,
+                    nullptr, 0, 1.0f, stream, &sc);
 }

@@ -639,8 +639,9 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_scatter
     const __nv_bfloat16* __restrict__ qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset,
     int D, const __nv_bfloat16* __restrict__ gq, const __nv_bfloat16* __restrict__ gk, const float2* __restrict__ tab,
     int Fg, int Hg, int Wg, int nf, int nh, int nw, float eps, PeerPtrs peers, int heads_per_peer, long long l_total,
-    int n_batch) {
-  __shared__ float red[3][ROW_NT / 32];
+    int n_batch, int which_mask) {
+  __shared__ float red[2][ROW_NT / 32];  // alternate per reduction: a buffer is rewritten two block syncs after its reads
+  int n_red = 0;
   const int nvec = D >> 3;
   const float inv_d = 1.0f / (float)D;
   const int half_d = nf + nh + nw;
@@ -668,6 +669,7 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_scatter
     }
 #pragma unroll 1
     for (int which = 0; which < 3; ++which) {
+      if (!((which_mask >> which) & 1)) continue;  // the caller scatters q, k, v in separate launches to overlap them
       const uint4* xr = reinterpret_cast<const uint4*>(qkv + row * ld + (long long)which * D);
       const uint4* gr = reinterpret_cast<const uint4*>(which == 0 ? gq : gk);
       // element offset of (which, b, pos, local head 0, 0) inside a peer's receive buffer
@@ -683,10 +685,9 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_scatter
         float ss = 0.f;
 #pragma unroll
         for (int i = 0; i < VPT; ++i) ss = vec_sumsq0(raw[i], ss);
-        const float r = rsqrtf(block_sum(ss, red[which]) * inv_d + eps);
+        const float r = rsqrtf(block_sum(ss, red[n_red & 1]) * inv_d + eps);
+        ++n_red;
         r2 = __floats2bfloat162_rn(r, r);
-      } else {
-        __syncthreads();  // red[0] / red[1] are rewritten by the next row only after everybody read them
       }
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
@@ -703,6 +704,90 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_scatter
       }
     }
   }
+}
+
+// Same producer with the stores handed to the TMA engine (round 2): results are staged in shared memory and leave as ONE
+// bulk store (cp.async.bulk shared -> global) per (row, matrix, peer) — a peer's heads are contiguous both in the row and
+// in its receive block, heads_per_peer * 256 bytes — instead of a 16-byte st.global from every thread.  The per-thread
+// stores put tens of thousands of NVLink-bound requests into the SM's load/store path; when this kernel runs on a side
+// stream UNDER a projection GEMM (sp.ulysses_qkv_attention_overlapped) those requests sit in front of the GEMM epilogue's
+// own stores.  Bulk stores queue in the TMA unit and drain at NVLink speed without occupying warps.  Two staging slots of
+// D*2 bytes (20 KB at D = 5120) fit beside the GEMM's 193 KB of shared memory.  Arithmetic identical: bit-identical results.
+template <int VPT>
+__global__ void __launch_bounds__(ROW_NT, 8) rmsnorm_rope_scatter_bulk_kernel(
+    const __nv_bfloat16* __restrict__ qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset,
+    int D, const __nv_bfloat16* __restrict__ gq, const __nv_bfloat16* __restrict__ gk, const float2* __restrict__ tab,
+    int Fg, int Hg, int Wg, int nf, int nh, int nw, float eps, PeerPtrs peers, int n_peers, int heads_per_peer,
+    long long l_total, int n_batch, int which_mask) {
+  extern __shared__ __align__(16) uint8_t stage[];  // 2 output staging slots, D*2 bytes each
+  __shared__ float red[2][ROW_NT / 32];
+  const int nvec = D >> 3;
+  const uint32_t row_bytes = (uint32_t)D * 2;
+  const uint32_t peer_bytes = row_bytes / (uint32_t)n_peers;  // heads_per_peer * head_dim * 2
+  const float inv_d = 1.0f / (float)D;
+  const int half_d = nf + nh + nw;
+  const float2* tab_f = tab;
+  const float2* tab_h = tab + (long long)Fg * nf;
+  const float2* tab_w = tab_h + (long long)Hg * nh;
+  const int j0 = ((threadIdx.x * 8) % (2 * half_d)) >> 1;
+  int seg = 0;  // segments (row, matrix) handled by this CTA so far: staging slot = seg & 1
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const long long b = row / rows_per_batch;
+    const long long pos = pos_offset + (row - b * rows_per_batch);
+    const bool rot = pos < (long long)Fg * Hg * Wg;
+    float2 cs[4];
+    if (rot) {
+      const int pw = (int)(pos % Wg);
+      const int ph = (int)((pos / Wg) % Hg);
+      const int pf = (int)(pos / ((long long)Wg * Hg));
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const int j = j0 + p;
+        if (j < nf) cs[p] = __ldg(tab_f + pf * nf + j);
+        else if (j < nf + nh) cs[p] = __ldg(tab_h + ph * nh + (j - nf));
+        else cs[p] = __ldg(tab_w + pw * nw + (j - nf - nh));
+      }
+    }
+#pragma unroll 1
+    for (int which = 0; which < 3; ++which) {
+      if (!((which_mask >> which) & 1)) continue;
+      const uint4* xr = reinterpret_cast<const uint4*>(qkv + row * ld + (long long)which * D);
+      const uint4* gr = reinterpret_cast<const uint4*>(which == 0 ? gq : gk);
+      uint4 raw[VPT];
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + ROW_NT * i;
+        raw[i] = (v < nvec) ? ld_stream(xr + v) : make_uint4(0, 0, 0, 0);
+      }
+      float ss = 0.f;
+      if (which < 2) {
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) ss = vec_sumsq0(raw[i], ss);
+      }
+      // staging slot seg & 1 was last used by segment seg - 2: its bulk stores must have read it out.  Thread 0 waits, the
+      // block-wide sync inside block_sum publishes that (for v the sum itself is unused).
+      if (threadIdx.x == 0) vc::bulk_wait_group_read<1>();
+      const float r = rsqrtf(block_sum(ss, red[seg & 1]) * inv_d + eps);
+      const __nv_bfloat162 r2 = __floats2bfloat162_rn(r, r);
+      uint4* os = reinterpret_cast<uint4*>(stage + (size_t)(seg & 1) * row_bytes);
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + ROW_NT * i;
+        if (v < nvec) os[v] = which < 2 ? rms_rope_vec(raw[i], r2, __ldg(gr + v), rot, cs) : raw[i];
+      }
+      vc::fence_proxy_async_smem();  // generic-proxy writes of the staging slot -> visible to the TMA engine
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        // element offset of (which, b, pos, local head 0, 0) in a peer's receive buffer; peer p gets row bytes [p*peer_bytes, ..)
+        const long long dst = ((((long long)which * n_batch + b) * l_total + pos) * heads_per_peer) * (2LL * half_d);
+        for (int p = 0; p < n_peers; ++p)
+          vc::bulk_store_1d(peers.p[p] + dst, stage + (size_t)(seg & 1) * row_bytes + (size_t)p * peer_bytes, peer_bytes);
+        vc::bulk_commit_group();
+      }
+      ++seg;
+    }
+  }
+  if (threadIdx.x == 0) vc::bulk_wait_group<0>();
 }
 
 // ----------------------------------------------------------------------------------------------------
@@ -911,8 +996,14 @@ int vc_rmsnorm_rope_qkv_scatter(const void* qkv, long long ld, long long rows, l
                                 long long pos_offset, int D, const void* gain_q, const void* gain_k,
                                 const void* rope_table, int grid_f, int grid_h, int grid_w, int nf, int nh, int nw,
                                 float eps, void* const* peer_recv, int n_peers, int heads_per_peer, long long l_total,
-                                void* stream) {
+                                int which_mask, void* stream) {
   VC_CHECK_ARG(qkv && gain_q && gain_k && rope_table && peer_recv, "vc_rmsnorm_rope_qkv_scatter: null pointer");
+  // which_mask: bits 0-2 select q / k / v; bit 3 (8) = bulk-store variant (stores issued by the TMA engine); bits 8-15 =
+  // cap on resident CTAs per SM for this launch (0 = default), used when the launch runs under a GEMM on another stream
+  const bool bulk = (which_mask & 8) != 0;
+  const int cta_cap = (which_mask >> 8) & 0xff;
+  which_mask &= 7;
+  VC_CHECK_ARG(which_mask >= 1, "vc_rmsnorm_rope_qkv_scatter: which_mask selects no matrix");
   VC_CHECK_ARG(n_peers >= 1 && n_peers <= 8, "vc_rmsnorm_rope_qkv_scatter: n_peers=%d must be in 1..8", n_peers);
   VC_CHECK_ARG(nf > 0 && nh > 0 && nw > 0 && (nf + nh + nw) % 4 == 0, "vc_rmsnorm_rope_qkv_scatter: bad rope split");
   const int hd = 2 * (nf + nh + nw);
@@ -927,12 +1018,29 @@ int vc_rmsnorm_rope_qkv_scatter(const void* qkv, long long ld, long long rows, l
   PeerPtrs pp;
   for (int i = 0; i < 8; ++i) pp.p[i] = (__nv_bfloat16*)(i < n_peers ? peer_recv[i] : nullptr);
   for (int i = 0; i < n_peers; ++i) VC_CHECK_ARG(pp.p[i] && (uintptr_t)pp.p[i] % 16 == 0, "vc_rmsnorm_rope_qkv_scatter: bad peer pointer %d", i);
+  int grid = grid_for_block_rows(rows);
+  if (cta_cap > 0 && grid > cta_cap * vc_host::sm_count()) grid = cta_cap * vc_host::sm_count();
+  if (bulk) {
+    int rcb = dispatch_vpt(D, [&](auto vpt) {
+      constexpr int V = decltype(vpt)::value;
+      const int smem = 2 * D * 2;
+      VC_ENSURE_DYN_SMEM((rmsnorm_rope_scatter_bulk_kernel<V>), smem, "vc_rmsnorm_rope_qkv_scatter");
+      const int cap8 = 8 * vc_host::sm_count();
+      rmsnorm_rope_scatter_bulk_kernel<V><<<grid < cap8 ? grid : cap8, ROW_NT, smem, (cudaStream_t)stream>>>(
+          (const __nv_bfloat16*)qkv, ld, rows, rows_per_batch, pos_offset, D, (const __nv_bfloat16*)gain_q,
+          (const __nv_bfloat16*)gain_k, (const float2*)rope_table, grid_f, grid_h, grid_w, nf, nh, nw, eps, pp, n_peers,
+          heads_per_peer, l_total, (int)(rows / rows_per_batch), which_mask);
+      return 0;
+    });
+    VC_CHECK_ARG(rcb == 0, "vc_rmsnorm_rope_qkv_scatter: unsupported D=%d", D);
+    VC_RETURN_LAUNCH_STATUS("vc_rmsnorm_rope_qkv_scatter");
+  }
   int rc = dispatch_vpt(D, [&](auto vpt) {
     constexpr int V = decltype(vpt)::value;
-    rmsnorm_rope_scatter_kernel<V><<<grid_for_block_rows(rows), ROW_NT, 0, (cudaStream_t)stream>>>(
+    rmsnorm_rope_scatter_kernel<V><<<grid, ROW_NT, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)qkv, ld, rows, rows_per_batch, pos_offset, D, (const __nv_bfloat16*)gain_q,
         (const __nv_bfloat16*)gain_k, (const float2*)rope_table, grid_f, grid_h, grid_w, nf, nh, nw, eps, pp,
-        heads_per_peer, l_total, (int)(rows / rows_per_batch));
+        heads_per_peer, l_total, (int)(rows / rows_per_batch), which_mask);
     return 0;
   });
   VC_CHECK_ARG(rc == 0, "vc_rmsnorm_rope_qkv_scatter: unsupported D=%d", D);

@@ -260,9 +260,10 @@ def _ptr_array(ptrs):
 
 
 def rmsnorm_rope_qkv_scatter(qkv, D, gain_q, gain_k, rows_per_batch, peer_ptrs, heads_per_peer, l_total, rope, grid,
-                             pos_offset=0, eps=1e-6):
+                             pos_offset=0, eps=1e-6, which_mask=7, bulk=False, cta_cap=0):
     """qkv [rows, 3D] of this rank's tokens -> RMSNorm+RoPE(q,k), v, written head-scattered into the peers' receive
-    buffers (device addresses `peer_ptrs`, layout [3, B, l_total, heads_per_peer, d])."""
+    buffers (device addresses `peer_ptrs`, layout [3, B, l_total, heads_per_peer, d]).  which_mask: bit 0 q, 1 k, 2 v.
+    bulk: stores issued by the TMA engine (one cp.async.bulk per row, matrix and peer); cta_cap: resident CTAs per SM."""
     global launch_count
     _chk(qkv, "qkv"); _chk(gain_q, "gain_q"); _chk(gain_k, "gain_k")
     assert qkv.dim() == 2 and qkv.shape[1] >= 3 * D
@@ -270,11 +271,29 @@ def rmsnorm_rope_qkv_scatter(qkv, D, gain_q, gain_k, rows_per_batch, peer_ptrs, 
     table, (nf, nh, nw) = rope
     gf, gh, gw = grid
     lib = _lib.load()
-    with _timed("rmsnorm_rope", 6.0 * rows * D):
+    with _timed("rmsnorm_rope", 4.0 * bin(which_mask & 7).count("1") * rows * D):
         _lib.check(lib.vc_rmsnorm_rope_qkv_scatter(_ptr(qkv), ld, rows, rows_per_batch, pos_offset, D, _ptr(gain_q),
                                                    _ptr(gain_k), _ptr(table), gf, gh, gw, nf, nh, nw, eps,
                                                    _ptr_array(peer_ptrs), len(peer_ptrs), heads_per_peer, l_total,
-                                                   _stream()), "vc_rmsnorm_rope_qkv_scatter")
+                                                   int(which_mask) | (8 if bulk else 0) | (int(cta_cap) << 8), _stream()),
+                   "vc_rmsnorm_rope_qkv_scatter")
+    launch_count += 1
+
+
+def gemm_scatter(a, w, bias, rows_per_batch, peer_ptrs, heads_per_peer, l_total, pos_offset=0, head_dim=128, sched=0):
+    """(a[M,K] @ w[N,K]^T + bias) with head h of row r stored into peer h // heads_per_peer's receive block
+    [n_batch, l_total, heads_per_peer, head_dim] (device addresses `peer_ptrs`) at token pos_offset + r % rows_per_batch:
+    a Linear and its Ulysses head-scatter in one kernel."""
+    global launch_count
+    _chk(a, "a"); _chk(w, "w"); _chk(bias, "bias")
+    assert a.dim() == 2 and w.dim() == 2 and a.shape[1] == w.shape[1], (a.shape, w.shape)
+    M, K = a.shape
+    N = w.shape[0]
+    lib = _lib.load()
+    with _timed("gemm", 2.0 * M * N * K):
+        _lib.check(lib.vc_gemm_bf16_scatter(_ptr(a), a.stride(0), _ptr(w), w.stride(0), M, N, K, _ptr(bias), rows_per_batch,
+                                            pos_offset, _ptr_array(peer_ptrs), len(peer_ptrs), heads_per_peer, head_dim,
+                                            l_total, int(sched), _stream()), "vc_gemm_bf16_scatter")
     launch_count += 1
 
 

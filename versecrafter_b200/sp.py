@@ -7,6 +7,8 @@ from xfuser's SeqAllToAll4D inside usp_attn_forward (not in the reference tree; 
 The layout transforms are plain tensor permutations so they run on any backend: NCCL over NVLink on the B200 box,
 gloo on CPU in tests/test_sp_cpu.py.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -71,6 +73,19 @@ class PeerExchange:
         self.rank = dist.get_rank(self.group)
         self.device = device
         self.bufs = {}
+        self._side = None
+        # schedule of ulysses_qkv_attention_overlapped (same arithmetic in every setting; tools/sp_overlap_ab.py measures them)
+        self.overlap_mode = os.environ.get("VC_SP_OVERLAP_MODE", "full")   # full | v_only
+        self.scatter_bulk = os.environ.get("VC_SP_SCATTER", "bulk") == "bulk"
+        self.scatter_cap = int(os.environ.get("VC_SP_SCATTER_CAP", "0"))
+        self.barrier_impl = os.environ.get("VC_SP_BARRIER", "own")         # own | torch
+        self._flags, self._status, self._epoch = None, None, 0
+
+    def side_stream(self):
+        """High-priority stream for the q / k scatter launches that run under the next GEMM (ulysses_qkv_attention_overlapped)."""
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=self.device, priority=-1)
+        return self._side
 
     def buffer(self, name, numel):
         """bf16 symmetric buffer of at least `numel` elements -> (tensor, [device address of every rank's copy])."""
@@ -83,7 +98,34 @@ class PeerExchange:
         return ent[0], ent[1]
 
     def barrier(self):
-        next(iter(self.bufs.values()))[2].barrier(channel=0)
+        """Stream-ordered barrier of the group.  Default: this library's epoch-flag kernel (vc_peer_barrier, one NVLink
+        round trip, csrc/peer_sync.cu); VC_SP_BARRIER=torch uses torch symmetric memory's barrier."""
+        from . import _lib, ops
+        with ops._timed("barrier", 0.0):
+            if self.barrier_impl == "torch":
+                next(iter(self.bufs.values()))[2].barrier(channel=0)
+                return
+            if self._flags is None:
+                t, ptrs = self.buffer("barrier_flags", 64)        # 128 bytes: 8 u32 epoch slots (+ padding) per rank
+                t.zero_()
+                self._status = torch.zeros(1, dtype=torch.int32, device=self.device)
+                torch.cuda.current_stream().synchronize()
+                self.bufs["barrier_flags"][2].barrier(channel=0)   # everybody's slots are zero before the first epoch
+                torch.cuda.current_stream().synchronize()
+                self._flags = ops._ptr_array(ptrs)
+            self._epoch += 1
+            lib = _lib.load()
+            _lib.check(lib.vc_peer_barrier(self._flags, self.rank, self.P, self._epoch & 0xFFFFFFFF, 0,
+                                           ops._ptr(self._status), ops._stream()), "vc_peer_barrier")
+            ops.launch_count += 1
+
+    def check_status(self):
+        """Raises if a barrier timed out (a peer never arrived).  Synchronises the current stream."""
+        from . import _lib
+        if self._status is not None:
+            v = int(self._status.item())
+            if v != 0:
+                raise _lib.VCError(f"sequence-parallel barrier timed out waiting for rank {v & 0xff} (status {v & 0xffffffff:#x})")
 
 
 def recv_layout_index(which, b, t, h, n_batch, l_total, heads_per_peer, head_dim):
@@ -111,7 +153,8 @@ def ulysses_attention_fused(px, qkv, B, Lp, H, d, gain_q, gain_k, rope, grid, ep
     n_recv, n_attn = 3 * B * L * Hp * d, B * Lp * D
     recv_t, recv_ptrs = px.buffer("qkv_recv", n_recv)
     attn_t, attn_ptrs = px.buffer("attn_recv", n_attn)
-    ops.rmsnorm_rope_qkv_scatter(qkv, D, gain_q, gain_k, Lp, recv_ptrs, Hp, L, rope, grid, pos_offset=rank * Lp, eps=eps)
+    ops.rmsnorm_rope_qkv_scatter(qkv, D, gain_q, gain_k, Lp, recv_ptrs, Hp, L, rope, grid, pos_offset=rank * Lp, eps=eps,
+                                 bulk=px.scatter_bulk)
     px.barrier()  # every peer's q/k/v slices have landed here; peers are done reading attn_recv of the previous block
     r = recv_t[:n_recv].view(3, B, L, Hp, d)
     head_off = rank * Hp * d * 2  # bytes: this rank's heads inside a peer's [.., H, d] row
@@ -119,4 +162,57 @@ def ulysses_attention_fused(px, qkv, B, Lp, H, d, gain_q, gain_k, rope, grid, ep
     ops.flash_attn_scatter(r[0], r[1][:, :Lk], r[2][:, :Lk], [p + head_off for p in attn_ptrs], Lp, (Lp * D, D, d),
                            variant=variant)
     px.barrier()  # every peer's head slices of my tokens have landed; peers are done reading their qkv_recv
+    return attn_t[:n_attn].view(B * Lp, D)
+
+
+def ulysses_qkv_attention_overlapped(px, h, wqkv, bqkv, qkv, B, Lp, H, d, gain_q, gain_k, rope, grid, eps, variant,
+                                     k_true=None):
+    """h [B*Lp, D] (LayerNorm+modulate output) -> self-attention output [B*Lp, H*d] (view of the symmetric buffer), with the
+    head-scatter all-to-alls hidden under the QKV projection instead of following it:
+        main stream                              side stream (high priority)
+        q = h Wq^T + bq          -> qkv[:, :D]
+        k = h Wk^T + bk          -> qkv[:, D:2D]   RMSNorm+RoPE(q) -> peers' buffers   (vc_rmsnorm_rope_qkv_scatter, mask q)
+        v = h Wv^T + bv -> peers' buffers          RMSNorm+RoPE(k) -> peers' buffers   (mask k)
+          (vc_gemm_bf16_scatter: v needs no norm, its exchange is the GEMM's epilogue)
+        barrier, attention (output rows stored to their owners), barrier
+    The NVLink stores of q and k (two thirds of the exchanged bytes) run while the tensor cores work on the next projection
+    and v never exists as a local matrix.  Arithmetic identical to ulysses_attention_fused (same kernels, same rounding)."""
+    from . import ops
+    P, rank = px.P, px.rank
+    Hp, L, D = H // P, P * Lp, H * d
+    n_recv, n_attn = 3 * B * L * Hp * d, B * Lp * D
+    recv_t, recv_ptrs = px.buffer("qkv_recv", n_recv)
+    attn_t, attn_ptrs = px.buffer("attn_recv", n_attn)
+    main, side = torch.cuda.current_stream(), px.side_stream()
+    scatter = dict(rows_per_batch=Lp, peer_ptrs=recv_ptrs, heads_per_peer=Hp, l_total=L, rope=rope, grid=grid,
+                   pos_offset=rank * Lp, eps=eps, bulk=px.scatter_bulk, cta_cap=px.scatter_cap)
+    v_block = 2 * B * L * Hp * d * 2  # bytes: offset of the v block inside a peer's [3, B, L, Hp, d] buffer
+    v_ptrs = [p + v_block for p in recv_ptrs]
+    if px.overlap_mode == "v_only":  # q|k as one GEMM and one scatter launch on this stream; only v rides in its GEMM
+        ops.gemm(h, wqkv[:2 * D], bqkv[:2 * D], out=qkv[:, :2 * D])
+        ops.gemm_scatter(h, wqkv[2 * D:], bqkv[2 * D:], Lp, v_ptrs, Hp, L, pos_offset=rank * Lp, head_dim=d)
+        ops.rmsnorm_rope_qkv_scatter(qkv, D, gain_q, gain_k, which_mask=3, **scatter)
+    else:
+        ops.gemm(h, wqkv[:D], bqkv[:D], out=qkv[:, :D])
+        ev_q = torch.cuda.Event()
+        ev_q.record(main)
+        ops.gemm(h, wqkv[D:2 * D], bqkv[D:2 * D], out=qkv[:, D:2 * D])
+        ev_k = torch.cuda.Event()
+        ev_k.record(main)
+        with torch.cuda.stream(side):
+            side.wait_event(ev_q)
+            ops.rmsnorm_rope_qkv_scatter(qkv, D, gain_q, gain_k, which_mask=1, **scatter)
+            side.wait_event(ev_k)
+            ops.rmsnorm_rope_qkv_scatter(qkv, D, gain_q, gain_k, which_mask=2, **scatter)
+            ev_s = torch.cuda.Event()
+            ev_s.record(side)
+        ops.gemm_scatter(h, wqkv[2 * D:], bqkv[2 * D:], Lp, v_ptrs, Hp, L, pos_offset=rank * Lp, head_dim=d)
+        main.wait_event(ev_s)
+    px.barrier()  # every peer's q/k/v slices have landed here; peers are done reading attn_recv of the previous block
+    r = recv_t[:n_recv].view(3, B, L, Hp, d)
+    head_off = rank * Hp * d * 2
+    Lk = L if k_true is None else min(k_true, L)
+    ops.flash_attn_scatter(r[0], r[1][:, :Lk], r[2][:, :Lk], [p + head_off for p in attn_ptrs], Lp, (Lp * D, D, d),
+                           variant=variant)
+    px.barrier()
     return attn_t[:n_attn].view(B * Lp, D)

@@ -209,6 +209,9 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         self.gradient_checkpointing = False
         self.sp_world_size, self.sp_world_rank, self.sp_group = 1, 0, None
         self._px, self._px_failed = None, False
+        # Ulysses: q / k head-scatter on a side stream under the next projection GEMM, v scattered by its GEMM's epilogue
+        # (sp.ulysses_qkv_attention_overlapped); VC_SP_OVERLAP=0 keeps the fused-QKV GEMM + one scatter kernel
+        self.sp_overlap = os.environ.get("VC_SP_OVERLAP", "1") != "0"
         self.attn_variant = int(os.environ.get("VC_ATTN_VARIANT", "4"))
         # cross-attention (512 text keys): the two-CTAs-per-SM short-key kernel (variant 6)
         self.xattn_variant = int(os.environ.get("VC_XATTN_VARIANT", "6"))
@@ -541,8 +544,16 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         h = self._buf("h", (rows, D))
         # self-attention half
         ops.ln_modulate(x2d, m[:, 0], m[:, 1], Lp, eps=self.eps, out=h)
-        qkv = ops.gemm(h, pk["wqkv"], pk["bqkv"], out=self._buf("qkv", (rows, 3 * D)))
         attn = self._buf("attn", (rows, D))
+        if self.sp_world_size > 1 and self._peer_exchange() is not None and self.sp_overlap and self.d == 128:
+            # Ulysses with the head-scatter hidden under the q / k / v projections (sp.ulysses_qkv_attention_overlapped)
+            attn_sa = sp.ulysses_qkv_attention_overlapped(
+                self._peer_exchange(), h, pk["wqkv"], pk["bqkv"], self._buf("qkv", (rows, 3 * D)), B, Lp, H, self.d,
+                sa.norm_q.weight, sa.norm_k.weight, st.rope, st.grid, self.eps, max(self.attn_variant, 2), k_true=st.l_true)
+            ops.gemm(attn_sa, sa.o.weight, sa.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_GATE | ops.EPI_RES, gate=m[:, 2],
+                     rows_per_batch=Lp, residual=x2d, out=x2d)
+            return self._block_tail(blk, x2d, m, ctx, st, h, attn)
+        qkv = ops.gemm(h, pk["wqkv"], pk["bqkv"], out=self._buf("qkv", (rows, 3 * D)))
         if self.sp_world_size > 1 and self._peer_exchange() is not None:
             # Ulysses with both all-to-alls fused into the producer kernels' stores over NVLink (sp.py)
             attn_sa = sp.ulysses_attention_fused(self._peer_exchange(), qkv, B, Lp, H, self.d, sa.norm_q.weight, sa.norm_k.weight,
@@ -738,6 +749,8 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
             self.record["head"] = yv
         if P > 1:
             yv = self.all_gather(yv, dim=1)
+            if self._peer_exchange() is not None:
+                self._peer_exchange().check_status()   # a timed-out cross-GPU barrier raises here instead of returning garbage
         out = torch.stack([ops.unpatchify(yv[b], grid, self.out_dim) for b in range(B)])
         if self.teacache is not None and cond_flag:
             self.teacache.cnt += 1
