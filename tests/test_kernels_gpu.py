@@ -265,6 +265,16 @@ def test_flash_attn_short_keys_x1(ops, B, H, Lq, Lk, fused):
     assert _attn_case(ops, B, H, Lq, Lk, 6, fused) < 1e-2
 
 
+@pytest.mark.parametrize("B,H,Lq,Lk", ATTN_SHAPES + [(2, 3, 1000, 512), (1, 2, 130, 1024), (2, 1, 640, 128), (1, 1, 7, 300),
+                                                     (1, 2, 200, 64), (1, 1, 129, 65), (2, 2, 256, 1)])
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("variant", [7, 8])
+def test_flash_attn_short_keys_x2(ops, B, H, Lq, Lk, fused, variant):
+    """variants 7 / 8: 64-key tiles with a double-buffered S (S_{j+1} computed during softmax_j), one 128-row Q tile per
+    CTA, two CTAs per SM; 8 = a quarter of the exponentials on the FMA pipe.  Odd / even / single tile counts, tails."""
+    assert _attn_case(ops, B, H, Lq, Lk, variant, fused) < 1e-2
+
+
 def test_flash_attn_large_scores_rescale(ops):
     """Rows whose running max keeps growing across key tiles exercise the O rescale path."""
     B, H, L, d = 1, 1, 1024, 128
@@ -272,7 +282,7 @@ def test_flash_attn_large_scores_rescale(ops):
     k = _rand((B, L, H, d), 26, 1.0)
     k = (k.float() * torch.linspace(0.2, 3.0, L, device="cuda")[None, :, None, None]).to(torch.bfloat16)
     v = _rand((B, L, H, d), 27)
-    for variant in (0, 1, 2, 3, 4, 5, 6):
+    for variant in (0, 1, 2, 3, 4, 5, 6, 7, 8):
         assert relerr(ops.flash_attn(q, k, v, variant=variant), restate.sdpa(q, k, v)) < 1e-2, variant
 
 

@@ -251,8 +251,11 @@ if __name__ == "__main__":
         for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "4").split(",")]:
             bench_attn(2, 40, 32760, 32760, variant)
     if "xattn" in which:  # cross-attention at the c3 launch shape: shared-S kernel (4) vs the short-key kernel (6)
-        for variant in (4, 6):
+        for variant in (4, 6, 7, 8):
             bench_attn(2, 40, 32760, 512, variant)
+        for variant in (6, 7, 8):   # c2's head count (12 heads) and a short prompt
+            bench_attn(2, 12, 32760, 512, variant)
+            bench_attn(2, 40, 32760, 192, variant)
     if "attn" in which:
         for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "0,1").split(",")]:
             bench_attn(1, 8, 32760, 32760, variant)

@@ -25,7 +25,6 @@ constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + BAR_BYTES + 1024;  // 
 constexpr int GROUP_M = 16;
 constexpr int EPI_WARPS = 8;
 constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;  // TMA warp, MMA warp, epilogue warps
-constexpr int DEFAULT_SCHED = 0;  // see vc_gemm_bf16: 0 single, 1 multicast cluster, 2 CTA pair
 
 enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_GATE = 4, EPI_RES = 8, EPI_SCALE = 16, EPI_SCATTER = 32, SCHED_MULTICAST = 64,
              SCHED_PAIR = 128, SCHED_SINGLE = 256 };
@@ -565,9 +564,16 @@ static int gemm_entry(const void* A, long long lda, const void* W, long long ldw
     if (e && !strcmp(e, "mc")) return 1;
     if (e && !strcmp(e, "pair")) return 2;
     const char* m = getenv("VC_GEMM_MC");
-    return (m && m[0] == '1') ? 1 : DEFAULT_SCHED;
+    return (m && m[0] == '1') ? 1 : -1;
   }();
-  int sched = (epilogue & SCHED_SINGLE) ? 0 : (epilogue & SCHED_PAIR) ? 2 : (epilogue & SCHED_MULTICAST) ? 1 : sched_env;
+  // Default per shape, from same-box measurements on B200 (profiles/gemm_sched_r02c.jsonl alone; profiles/bench_c3_r02b_abab_*,
+  // bench_c2_r02c_*, gpurun N=2 ABAB in the step): the CTA pair is faster alone at every c3 / c2 shape but one (+4..+15 %,
+  // +11..+15 % at the M = 8190 rows of an 8-GPU rank) and wins inside the step at c2 (743 vs 758 ms) and under sequence
+  // parallelism (2 GPUs: 2135 vs 2152 ms); inside the single-GPU c3 step (M = 65520, K >= 5120) the chip sits on its power
+  // cap, the pair's GEMMs gain 5 % and self-attention loses 5 % of its clock, and the step is 1 % slower (4280 vs 4237 ms).
+  const int sched_auto = (M > 40000 && K >= 4096) ? 0 : 2;
+  int sched = (epilogue & SCHED_SINGLE) ? 0 : (epilogue & SCHED_PAIR) ? 2 : (epilogue & SCHED_MULTICAST) ? 1
+              : sched_env >= 0 ? sched_env : sched_auto;
   if (M <= BM) sched = 0;  // the paired schedules need two M tiles
   const bool mc = sched != 0;
   CUtensorMap ta, tb;

@@ -76,7 +76,7 @@ class PeerExchange:
         self._side = None
         # schedule of ulysses_qkv_attention_overlapped (same arithmetic in every setting; tools/sp_overlap_ab.py measures them)
         self.overlap_mode = os.environ.get("VC_SP_OVERLAP_MODE", "full")   # full | v_only
-        self.scatter_bulk = os.environ.get("VC_SP_SCATTER", "bulk") == "bulk"
+        self.scatter_bulk = os.environ.get("VC_SP_SCATTER", "st") == "bulk"  # per-thread stores measured faster
         self.scatter_cap = int(os.environ.get("VC_SP_SCATTER_CAP", "0"))
         self.barrier_impl = os.environ.get("VC_SP_BARRIER", "own")         # own | torch
         self._flags, self._status, self._epoch = None, None, 0

@@ -209,12 +209,14 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         self.gradient_checkpointing = False
         self.sp_world_size, self.sp_world_rank, self.sp_group = 1, 0, None
         self._px, self._px_failed = None, False
-        # Ulysses: q / k head-scatter on a side stream under the next projection GEMM, v scattered by its GEMM's epilogue
-        # (sp.ulysses_qkv_attention_overlapped); VC_SP_OVERLAP=0 keeps the fused-QKV GEMM + one scatter kernel
-        self.sp_overlap = os.environ.get("VC_SP_OVERLAP", "1") != "0"
+        # Ulysses exchange schedule.  Default: fused-QKV GEMM + ONE scatter kernel.  VC_SP_OVERLAP=1: q / k head-scatter on
+        # a side stream under the next projection GEMM, v scattered by its GEMM's epilogue
+        # (sp.ulysses_qkv_attention_overlapped) — bit-identical, but measured no faster on 2 GPUs at c3: the remote stores
+        # slow the GEMM they hide behind by as much as they cost alone (profiles/sp_overlap_ab_n2_r02.jsonl), so it is opt-in
+        self.sp_overlap = os.environ.get("VC_SP_OVERLAP", "0") == "1"
         self.attn_variant = int(os.environ.get("VC_ATTN_VARIANT", "4"))
-        # cross-attention (512 text keys): the two-CTAs-per-SM short-key kernel (variant 6)
-        self.xattn_variant = int(os.environ.get("VC_XATTN_VARIANT", "6"))
+        # cross-attention (512 text keys): two-CTAs-per-SM short-key kernel with 64-key tiles and a double-buffered S (variant 7)
+        self.xattn_variant = int(os.environ.get("VC_XATTN_VARIANT", "7"))
         self.implicit_patch_embed = os.environ.get("VC_PATCH_EMBED", "implicit") != "explicit"
         self._ws = {}
         self._rope_cache = {}
