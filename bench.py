@@ -342,9 +342,8 @@ def run_gpu_arm(args):
         for _ in range(2):
             step_resident()             # re-warm after the workspace release
 
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
+    sampler = ClockSampler(local_rank)   # every rank samples its own GPU; rank 0's goes into `clocks`, all into `per_rank`
+    sampler.start()
     # headline: K steps with nothing but the kernels on the stream; the per-kernel CUDA events (two per launch, ~2,000 per
     # step) go into a separate instrumented pass right after, inside the same clock-sampled region
     ops.launch_count = 0
@@ -354,7 +353,15 @@ def run_gpu_arm(args):
     ops.timing = {}
     ms_inst, _ = timed(step_resident, args.steps)   # same K steps again, every launch bracketed by CUDA events
     timing, ops.timing = ops.timing, None
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop()
+    # host side: wall time the Python / ctypes path needs to ENQUEUE one forward on an idle stream (the launch queue holds
+    # the ~1,000 launches of a step, so the call returns before the GPU is done) — the host is the limit only if this
+    # approaches the device time of a step
+    torch.cuda.synchronize()
+    t_h = time.perf_counter()
+    step_resident()
+    host_ms = (time.perf_counter() - t_h) * 1e3
+    torch.cuda.synchronize()
     # end to end through the public forward() with host buffers
     step_e2e()
     ms_e2e, y_host = timed(step_e2e, args.steps)
@@ -365,6 +372,19 @@ def run_gpu_arm(args):
     h2d = host["x"].numel() * 2 + host["geo"].numel() * 2 + sum(c.numel() * 2 for c in host["ctx"]) + host["t"].numel() * 4
     d2h = y_host.numel() * y_host.element_size()
     kern = summarize_timing(timing, peaks)
+    per_rank = None
+    if world > 1:
+        # which GPU the others wait for: device ms per step of every kernel class on every rank (instrumented pass) and each
+        # GPU's median SM clock.  Sequence parallelism runs in lock step (two barriers per block), so the step is the
+        # slowest rank's compute; a rank's `barrier` time is its own wait for that rank.
+        names = sorted(kern)
+        mine = torch.tensor([kern[n]["ms_total"] / args.steps for n in names] + [float(clocks["sm_mhz"] or 0.0)],
+                            device="cuda", dtype=torch.float64)
+        allr = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        tab = torch.stack(allr).cpu()
+        per_rank = {n: [round(float(v), 2) for v in tab[:, i]] for i, n in enumerate(names)}
+        per_rank["sm_mhz"] = [float(v) for v in tab[:, -1]]
     gemm_f, attn_f = work_per_step(cfg, L, B)
     dom = kern.get("attn_self", {})
     # dominant kernel: self-attention (52 % of the step's FLOPs at c3); algorithmic flops per launch = 4*B*(H/P)*L^2*128
@@ -397,9 +417,10 @@ def run_gpu_arm(args):
             "clocks": clocks,
             "e2e": {"value": tokens / (ms_e2e / args.steps / 1e3), "unit": "tokens/s", "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-            "gpu_launches": launches}
+            "gpu_launches": launches, "host_enqueue_ms_per_step": host_ms}
     if sp_parity is not None:
         line["sp_parity"] = sp_parity
+        line["per_rank_ms_per_step"] = per_rank
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             try:
@@ -408,6 +429,8 @@ def run_gpu_arm(args):
                 line["cpu_baseline"] = {"error": repr(e)[:200]}
         print(json.dumps(line), flush=True)
     if world > 1:
+        if model._peer_exchange() is not None:
+            model._peer_exchange().check_status(wait=True)   # no cross-GPU barrier of the run timed out
         dist.destroy_process_group()
 
 

@@ -98,7 +98,10 @@ int vc_modulation_table(const void* const* block_modulations, int n_blocks, cons
  *   degree-3 polynomial on the FMA pipe instead of the MUFU (rel. error < 1e-4, below P's bf16 rounding).
  *   4 is the fastest on B200 under the power cap and is what the drop-in module uses for self-attention.
  *   6: short key sequences (cross-attention to the 512 text tokens): one 128-row Q tile per CTA, 256 TMEM columns,
- *   96 KB smem, so two CTAs share an SM and each one's prologue/epilogue hides behind the other's MMAs. */
+ *   96 KB smem, so two CTAs share an SM and each one's prologue/epilogue hides behind the other's MMAs.
+ *   7 / 8: 6 with 64-key tiles and S double-buffered inside the same 256 TMEM columns (S_j+1 is computed during
+ *   softmax_j); 8 moves a quarter of the exp2 to the FMA pipe.  9: the pipeline of 7 in a persistent CTA (2 per SM) that
+ *   walks Q tiles: barriers / TMEM set up once, next Q prefetched, O drained under the next tile's S MMAs. */
 int vc_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, int B, int H, int Lq, int Lk,
                       int head_dim, const long long* q_strides, const long long* k_strides,
                       const long long* v_strides, const long long* o_strides, float softmax_scale, int variant,

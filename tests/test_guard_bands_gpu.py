@@ -109,7 +109,7 @@ def test_rmsnorm_rope_guard_bands(ops, D, H):
         assert g1.intact(), kw
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6, 7, 8])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6, 7, 8, 9])
 @pytest.mark.parametrize("Lq,Lk", [(333, 333), (129, 515), (37, 5)])
 def test_flash_attn_guard_bands(ops, variant, Lq, Lk):
     B, H, d = 2, 3, 128

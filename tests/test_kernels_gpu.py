@@ -268,11 +268,24 @@ def test_flash_attn_short_keys_x1(ops, B, H, Lq, Lk, fused):
 @pytest.mark.parametrize("B,H,Lq,Lk", ATTN_SHAPES + [(2, 3, 1000, 512), (1, 2, 130, 1024), (2, 1, 640, 128), (1, 1, 7, 300),
                                                      (1, 2, 200, 64), (1, 1, 129, 65), (2, 2, 256, 1)])
 @pytest.mark.parametrize("fused", [False, True])
-@pytest.mark.parametrize("variant", [7, 8])
+@pytest.mark.parametrize("variant", [7, 8, 9])
 def test_flash_attn_short_keys_x2(ops, B, H, Lq, Lk, fused, variant):
     """variants 7 / 8: 64-key tiles with a double-buffered S (S_{j+1} computed during softmax_j), one 128-row Q tile per
-    CTA, two CTAs per SM; 8 = a quarter of the exponentials on the FMA pipe.  Odd / even / single tile counts, tails."""
+    CTA, two CTAs per SM; 8 = a quarter of the exponentials on the FMA pipe; 9 = the same pipeline in a persistent CTA
+    that walks Q tiles.  Odd / even / single tile counts, tails."""
     assert _attn_case(ops, B, H, Lq, Lk, variant, fused) < 1e-2
+
+
+@pytest.mark.parametrize("Lk", [512, 192, 65])
+def test_flash_attn_persistent_x3_many_tiles_per_cta(ops, Lk):
+    """variant 9 with far more Q tiles than resident CTAs (2 per SM), so every CTA walks several tiles: odd and even key-tile
+    counts flip the ring parity between consecutive tiles; bit-identical to variant 7 (same arithmetic per tile)."""
+    B, H, Lq, d = 2, 6, 128 * 61 + 37, 128          # 2 * 6 * 62 = 744 tiles on 296 CTAs
+    q, k, v = _rand((B, Lq, H, d), 31), _rand((B, Lk, H, d), 32), _rand((B, Lk, H, d), 33)
+    o9 = ops.flash_attn(q, k, v, variant=9)
+    o7 = ops.flash_attn(q, k, v, variant=7)
+    assert torch.equal(o9, o7)
+    assert relerr(o9, restate.sdpa(q, k, v)) < 1e-2
 
 
 def test_flash_attn_large_scores_rescale(ops):
@@ -282,7 +295,7 @@ def test_flash_attn_large_scores_rescale(ops):
     k = _rand((B, L, H, d), 26, 1.0)
     k = (k.float() * torch.linspace(0.2, 3.0, L, device="cuda")[None, :, None, None]).to(torch.bfloat16)
     v = _rand((B, L, H, d), 27)
-    for variant in (0, 1, 2, 3, 4, 5, 6, 7, 8):
+    for variant in (0, 1, 2, 3, 4, 5, 6, 7, 8, 9):
         assert relerr(ops.flash_attn(q, k, v, variant=variant), restate.sdpa(q, k, v)) < 1e-2, variant
 
 

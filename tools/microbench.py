@@ -236,7 +236,9 @@ if __name__ == "__main__":
     if "rows_ab" in which:
         bench_rows_ab()
         bench_rows_ab(D=1536)
-    if "gemm_sched" in which:
+    if "gemm_sched" in which and os.environ.get("VC_MB_GEMM_ONE"):   # one shape only (ncu capture of the pair kernel)
+        bench_gemm_sched(65520, 15360, 5120, "bias")
+    elif "gemm_sched" in which:
         for (M, N, K, epi) in [(65520, 15360, 5120, "bias"), (65520, 5120, 5120, "gate_res"), (65520, 13824, 5120, "gelu"),
                                (65520, 5120, 13824, "gate_res"), (65520, 4608, 1536, "bias"), (65520, 8960, 1536, "gelu"),
                                (65520, 1536, 8960, "gate_res"), (8190, 15360, 5120, "bias"), (8190, 5120, 13824, "gate_res")]:
@@ -251,9 +253,9 @@ if __name__ == "__main__":
         for variant in [int(v) for v in os.environ.get("VC_ATTN_VARIANTS", "4").split(",")]:
             bench_attn(2, 40, 32760, 32760, variant)
     if "xattn" in which:  # cross-attention at the c3 launch shape: shared-S kernel (4) vs the short-key kernel (6)
-        for variant in (4, 6, 7, 8):
+        for variant in (4, 6, 7, 8, 9):
             bench_attn(2, 40, 32760, 512, variant)
-        for variant in (6, 7, 8):   # c2's head count (12 heads) and a short prompt
+        for variant in (6, 7, 9):   # c2's head count (12 heads) and a short prompt
             bench_attn(2, 12, 32760, 512, variant)
             bench_attn(2, 40, 32760, 192, variant)
     if "attn" in which:

@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 timeout 300 $TR --master-port 29601 tools/sp_check.py > gpurun_out/mg${N}_sp_check.log 2>&1; echo "sp_check rc=$?"; grep "^sp_check" gpurun_out/mg${N}_sp_check.log
 for c in c3 c4; do
-  timeout 900 $TR --master-port 29602 bench.py --gpus $N --config $c --steps 4 --warmup 3 2> gpurun_out/mg${N}_bench_$c.err | grep '^{' > gpurun_out/mg${N}_bench_$c.json; echo "bench $c rc=$?"
+  timeout 900 $TR --master-port 29602 bench.py --gpus $N --config $c --steps 3 --warmup 3 2> gpurun_out/mg${N}_bench_$c.err | grep '^{' > gpurun_out/mg${N}_bench_$c.json; echo "bench $c rc=$?"
   python - <<P
 import json
 d=json.load(open('gpurun_out/mg${N}_bench_$c.json')); k=d['kernels']

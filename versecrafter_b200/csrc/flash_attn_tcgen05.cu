@@ -1201,6 +1201,299 @@ int launch_x2(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& t
   return 0;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Variant 9 ("x3", persistent short-key kernel, round 2).  Timing variant 7 at Lk = 192 vs 512 showed 1.3 k cycles per
+// 64-key step but 12.6 k cycles of un-overlapped prologue + epilogue per CTA (barrier init, TMEM allocation, Q from HBM,
+// O to HBM, launch): 54 % of the kernel at Lk = 512.  Here the same pipeline (64-key tiles, S0 | S1 | O in 256 TMEM
+// columns, two CTAs per SM) runs in a PERSISTENT CTA that walks Q tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...:
+//   * barriers and TMEM are set up once;
+//   * the single Q buffer is refilled for tile t+1 as soon as the last S MMA of tile t has read it (q_empty = commit after
+//     S_{n-1}), i.e. about two softmax steps + the epilogue ahead of its first use;
+//   * the MMA warp issues S_0 / S_1 of tile t+1 while the softmax warps still drain O of tile t; only PV_0 of tile t+1
+//     (which overwrites O) waits for that epilogue (o_empty).
+// All ring indices run on global counters (g = t_local * nk + j), so odd tile counts need no special case.
+// ---------------------------------------------------------------------------------------------------------------
+template <int kPoly>
+__global__ void __launch_bounds__(X1_THREADS, 2)
+flash_attn_x3_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                     const __grid_constant__ CUtensorMap tmV, const AttnParams p, int H, int n_qblk, int n_tiles) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + TILE_BYTES;               // 2 slots
+  uint8_t* sV = sK + 2 * X2_KV_BYTES;            // 2 slots
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 2 * X2_KV_BYTES);
+  uint64_t* q_full = bars;            // 1
+  uint64_t* q_empty = bars + 1;       // 1
+  uint64_t* k_full = bars + 2;        // 2
+  uint64_t* k_empty = k_full + 2;     // 2
+  uint64_t* v_full = k_empty + 2;     // 2
+  uint64_t* v_empty = v_full + 2;     // 2
+  uint64_t* s_full = v_empty + 2;     // 2
+  uint64_t* p_ready = s_full + 2;     // 2
+  uint64_t* pv_done = p_ready + 2;    // 2
+  uint64_t* o_full = pv_done + 2;     // 1
+  uint64_t* o_empty = o_full + 1;     // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nk = (p.Lk + X2_BKV - 1) / X2_BKV;
+
+  if (threadIdx.x == 0) {
+    vc::mbar_init(q_full, 1);
+    vc::mbar_init(q_empty, 1);
+    for (int i = 0; i < 2; ++i) {
+      vc::mbar_init(&k_full[i], 1);
+      vc::mbar_init(&k_empty[i], 1);
+      vc::mbar_init(&v_full[i], 1);
+      vc::mbar_init(&v_empty[i], 1);
+      vc::mbar_init(&s_full[i], 1);
+      vc::mbar_init(&p_ready[i], 128);
+      vc::mbar_init(&pv_done[i], 1);
+    }
+    vc::mbar_init(o_full, 1);
+    vc::mbar_init(o_empty, 128);
+    vc::fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    vc::tma_prefetch_desc(&tmQ);
+    vc::tma_prefetch_desc(&tmK);
+    vc::tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1) vc::tmem_alloc(tmem_slot, 256);
+  vc::tc_fence_before();
+  __syncthreads();
+  vc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // tile -> (query block, head, batch): query blocks of one (batch, head) are consecutive so co-running CTAs share K/V in L2
+  auto decode = [&](int t, int& q_blk, int& head, int& batch) {
+    q_blk = t % n_qblk;
+    const int bh = t / n_qblk;
+    head = bh % H;
+    batch = bh / H;
+  };
+
+  if (warp == 0) {
+    if (vc::elect_one()) {
+      int tl = 0;  // local tile counter
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+        int q_blk, head, batch;
+        decode(t, q_blk, head, batch);
+        const int g0 = tl * nk;
+        auto load_k = [&](int j) {
+          const int g = g0 + j, slot = g & 1;
+          vc::mbar_wait(&k_empty[slot], ((g >> 1) & 1) ^ 1);
+          vc::mbar_expect_tx(&k_full[slot], X2_KV_BYTES);
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            vc::tma_load_4d(sK + slot * X2_KV_BYTES + h * X2_KV_HALF, &tmK, &k_full[slot], h * 64, j * X2_BKV, head, batch);
+        };
+        auto load_v = [&](int j) {
+          const int g = g0 + j, slot = g & 1;
+          vc::mbar_wait(&v_empty[slot], ((g >> 1) & 1) ^ 1);
+          vc::mbar_expect_tx(&v_full[slot], X2_KV_BYTES);
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            vc::tma_load_4d(sV + slot * X2_KV_BYTES + h * X2_KV_HALF, &tmV, &v_full[slot], h * 64, j * X2_BKV, head, batch);
+        };
+        vc::mbar_wait(q_empty, (tl & 1) ^ 1);   // the S MMAs of the previous tile have read Q
+        vc::mbar_expect_tx(q_full, TILE_BYTES);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) vc::tma_load_4d(sQ + h * HALF_BYTES, &tmQ, q_full, h * 64, q_blk * BQ, head, batch);
+        load_k(0);
+        if (nk > 1) load_k(1);
+        for (int j = 0; j < nk; ++j) {
+          load_v(j);
+          if (j + 2 < nk) load_k(j + 2);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (vc::elect_one()) {
+      constexpr uint32_t idesc_s = vc::umma_idesc_bf16(BQ, X2_BKV, 0, 0);
+      constexpr uint32_t idesc_o = vc::umma_idesc_bf16(BQ, HD, 0, 1);
+      const uint32_t qa = vc::smem_u32(sQ);
+      int tl = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+        const int g0 = tl * nk;
+        auto issue_s = [&](int j) {
+          const int g = g0 + j, b = g & 1;
+          vc::mbar_wait(&k_full[b], (g >> 1) & 1);
+          vc::tc_fence_after();
+          const uint32_t ka = vc::smem_u32(sK + b * X2_KV_BYTES);
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k) {
+            const uint32_t qoff = (k >> 2) * HALF_BYTES + (k & 3) * 32;
+            const uint32_t koff = (k >> 2) * X2_KV_HALF + (k & 3) * 32;
+            vc::umma_ss(tmem_base + b * X2_BKV, vc::umma_desc_sw128(qa + qoff, 16, 1024),
+                        vc::umma_desc_sw128(ka + koff, 16, 1024), idesc_s, k != 0 ? 1u : 0u);
+          }
+          vc::umma_commit(&s_full[b]);
+          vc::umma_commit(&k_empty[b]);
+          if (j == nk - 1) vc::umma_commit(q_empty);   // last reader of this tile's Q
+        };
+        vc::mbar_wait(q_full, tl & 1);
+        issue_s(0);
+        if (nk > 1) issue_s(1);
+        for (int j = 0; j < nk; ++j) {
+          const int g = g0 + j, b = g & 1;
+          vc::mbar_wait(&v_full[b], (g >> 1) & 1);
+          vc::mbar_wait(&p_ready[b], (g >> 1) & 1);
+          if (j == 0) vc::mbar_wait(o_empty, (tl & 1) ^ 1);   // the previous tile's O has been read out
+          vc::tc_fence_after();
+          const uint32_t va = vc::smem_u32(sV + b * X2_KV_BYTES);
+#pragma unroll
+          for (int k = 0; k < X2_BKV / 16; ++k)
+            vc::umma_ts(tmem_base + 128, tmem_base + b * X2_BKV + k * 8, vc::umma_desc_sw128(va + k * 2048, X2_KV_HALF, 1024),
+                        idesc_o, (j != 0 || k != 0) ? 1u : 0u);
+          vc::umma_commit(&v_empty[b]);
+          vc::umma_commit(&pv_done[b]);
+          if (j + 2 < nk) issue_s(j + 2);
+        }
+        vc::umma_commit(o_full);
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_bits = static_cast<uint32_t>(quarter * 32) << 16;
+    const uint32_t o_addr = tmem_base + 128 + lane_bits;
+    const float sl2 = p.scale_log2;
+    int tl = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+      int q_blk, head, batch;
+      decode(t, q_blk, head, batch);
+      const int g0 = tl * nk;
+      float m_run = -INFINITY, l_run = 0.f;
+      for (int j = 0; j < nk; ++j) {
+        const int g = g0 + j, b = g & 1;
+        const uint32_t s_addr = tmem_base + b * X2_BKV + lane_bits;
+        vc::mbar_wait(&s_full[b], (g >> 1) & 1);
+        vc::tc_fence_after();
+        uint32_t s[64];
+        vc::tmem_ld32(s_addr, s);
+        vc::tmem_ld32(s_addr + 32, s + 32);
+        vc::tmem_ld_wait();
+        if (j == nk - 1) {
+          const int valid = p.Lk - j * X2_BKV;
+          if (valid < X2_BKV) {
+#pragma unroll
+            for (int i = 0; i < 64; ++i)
+              if (i >= valid) s[i] = __float_as_uint(-INFINITY);
+          }
+        }
+        float mx[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) mx[i] = __uint_as_float(s[i]);
+#pragma unroll
+        for (int i = 8; i < 64; ++i) mx[i & 7] = fmaxf(mx[i & 7], __uint_as_float(s[i]));
+        const float mt = fmaxf(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])), fmaxf(fmaxf(mx[4], mx[5]), fmaxf(mx[6], mx[7])));
+        const float m_new = fmaxf(m_run, mt);
+        const bool need = (m_new - m_run) * sl2 > RESCALE_THRESHOLD;
+        if (__any_sync(0xffffffffu, need)) {
+          const float alpha = fast_exp2((m_run - m_new) * sl2);
+          l_run *= alpha;
+          m_run = m_new;
+          if (j > 0) {
+            const int gp = g - 1;   // O must be idle: PV_{j-1} may still run; PV_j waits for our p_ready arrival
+            vc::mbar_wait(&pv_done[gp & 1], (gp >> 1) & 1);
+            vc::tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+              uint32_t o[32];
+              vc::tmem_ld32(o_addr + c * 32, o);
+              vc::tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              vc::tmem_st32(o_addr + c * 32, o);
+            }
+            vc::tmem_st_wait();
+          }
+        }
+        const float mb = m_run * sl2;
+        float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float p0, p1;
+          if (i < kPoly / 2) {
+            exp2_poly2(p0, p1, fmaf(__uint_as_float(s[2 * i]), sl2, -mb), fmaf(__uint_as_float(s[2 * i + 1]), sl2, -mb));
+          } else {
+            p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -mb));
+            p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -mb));
+          }
+          sum0 += p0;
+          sum1 += p1;
+          s[i] = vc::pack_bf16x2(p0, p1);
+        }
+        vc::tmem_st32(s_addr, s);
+        vc::tmem_st_wait();
+        l_run += sum0 + sum1;
+        vc::tc_fence_before();
+        vc::mbar_arrive(&p_ready[b]);
+      }
+
+      vc::mbar_wait(o_full, tl & 1);
+      vc::tc_fence_after();
+      const float inv_l = 1.0f / l_run;
+      const int q_row = q_blk * BQ + row;
+      __nv_bfloat16* orow = p.O + (long long)batch * p.o_stride_b + (long long)q_row * p.o_stride_l +
+                            (long long)head * p.o_stride_h;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[32];
+        vc::tmem_ld32(o_addr + c * 32, o);
+        vc::tmem_ld_wait();
+        if (c == 3) {   // O is in registers: the next tile's PV_0 may overwrite the accumulator
+          vc::tc_fence_before();
+          vc::mbar_arrive(o_empty);
+        }
+        if (q_row < p.Lq) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 u;
+            u.x = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 0]) * inv_l, __uint_as_float(o[g * 8 + 1]) * inv_l);
+            u.y = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 2]) * inv_l, __uint_as_float(o[g * 8 + 3]) * inv_l);
+            u.z = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 4]) * inv_l, __uint_as_float(o[g * 8 + 5]) * inv_l);
+            u.w = vc::pack_bf16x2(__uint_as_float(o[g * 8 + 6]) * inv_l, __uint_as_float(o[g * 8 + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(orow + c * 32 + g * 8) = u;
+          }
+        }
+      }
+    }
+  }
+
+  vc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) vc::tmem_dealloc(tmem_base, 256);
+}
+
+template <int kPoly>
+int launch_x3(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p, int B, int H,
+              cudaStream_t s) {
+  VC_ENSURE_DYN_SMEM((flash_attn_x3_kernel<kPoly>), X2_SMEM_BYTES, "vc_flash_attn_fwd");
+  {
+    static bool carve[vc_host::kMaxDevices] = {};
+    const int dev = vc_host::current_device();
+    if (!carve[dev]) {
+      cudaError_t e = cudaFuncSetAttribute(flash_attn_x3_kernel<kPoly>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+      if (e != cudaSuccess) {
+        vc_host::set_error("vc_flash_attn_fwd: cannot set the shared-memory carve-out: %s", cudaGetErrorString(e));
+        return (int)e;
+      }
+      carve[dev] = true;
+    }
+  }
+  const int n_qblk = (p.Lq + BQ - 1) / BQ;
+  const long long tiles = (long long)n_qblk * H * B;
+  const int cap = 2 * vc_host::sm_count();   // two resident CTAs per SM
+  const int grid = (int)(tiles < cap ? tiles : cap);
+  flash_attn_x3_kernel<kPoly><<<grid, X1_THREADS, X2_SMEM_BYTES, s>>>(tq, tk, tv, p, H, n_qblk, (int)tiles);
+  return 0;
+}
+
 }  // namespace
 
 // strides are in ELEMENTS: (batch, token, head); the head_dim axis must be contiguous (stride 1), head_dim == 128.
@@ -1211,9 +1504,9 @@ static int attn_impl(const void* q, const void* k, const void* v, void* o, int B
   VC_CHECK_ARG(q && k && v && o && q_strides && k_strides && v_strides && o_strides, "vc_flash_attn_fwd: null pointer");
   VC_CHECK_ARG(head_dim == HD, "vc_flash_attn_fwd: head_dim %d unsupported (only 128)", head_dim);
   VC_CHECK_ARG(B > 0 && H > 0 && Lq >= 0 && Lk > 0, "vc_flash_attn_fwd: bad sizes B=%d H=%d Lq=%d Lk=%d", B, H, Lq, Lk);
-  VC_CHECK_ARG(variant >= 0 && variant <= 8,
-               "vc_flash_attn_fwd: variant must be 0 (P in smem), 1 (P in TMEM over S), 2-5 (shared S buffer), 6 (short-key x1) or "
-               "7/8 (short-key x2, double-buffered 64-key S)");
+  VC_CHECK_ARG(variant >= 0 && variant <= 9,
+               "vc_flash_attn_fwd: variant must be 0 (P in smem), 1 (P in TMEM over S), 2-5 (shared S buffer), 6 (short-key x1), "
+               "7/8 (short-key x2, double-buffered 64-key S) or 9 (persistent x3)");
   const long long* all[4] = {q_strides, k_strides, v_strides, o_strides};
   for (int t = 0; t < 4; ++t)
     for (int i = 0; i < 3; ++i)
@@ -1241,6 +1534,7 @@ static int attn_impl(const void* q, const void* k, const void* v, void* o, int B
     case 6: rc = launch_x1(tq, tk, tv, p, B, H, st); break;
     case 7: rc = launch_x2<0>(tq, tk, tv, p, B, H, st); break;
     case 8: rc = launch_x2<16>(tq, tk, tv, p, B, H, st); break;
+    case 9: rc = launch_x3<0>(tq, tk, tv, p, B, H, st); break;
     case 0: rc = launch<false>(tq, tk, tv, p, grid, st); break;
     case 1: rc = launch<true>(tq, tk, tv, p, grid, st); break;
     case 2: rc = launch_sa<false, 0>(tq, tk, tv, p, grid, st); break;

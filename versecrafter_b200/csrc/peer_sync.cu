@@ -18,6 +18,9 @@ __global__ void __launch_bounds__(32, 1) peer_barrier_kernel(FlagPtrs flags, int
                                                              unsigned long long timeout_ns, unsigned int* status) {
   const int p = threadIdx.x;
   if (p >= n_peers) return;
+  // an earlier barrier of this group timed out: the step is lost; publish the epoch (peers may still be waiting) but do not
+  // spend another timeout in each of the remaining barriers of the forward
+  const bool failed = *reinterpret_cast<volatile unsigned int*>(status) != 0u;
   __threadfence_system();
   if (p != rank) {
     unsigned int* remote = flags.p[p] + rank;
@@ -29,7 +32,7 @@ __global__ void __launch_bounds__(32, 1) peer_barrier_kernel(FlagPtrs flags, int
     int spins = 0;
     while (true) {
       asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(seen) : "l"(mine) : "memory");
-      if ((int)(seen - epoch) >= 0) break;  // wrap-safe: the peer is at this epoch or beyond
+      if ((int)(seen - epoch) >= 0 || failed) break;  // wrap-safe: the peer is at this epoch or beyond
       if ((++spins & 1023) == 0) {
         unsigned long long t1;
         asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t1));

@@ -80,6 +80,7 @@ class PeerExchange:
         self.scatter_cap = int(os.environ.get("VC_SP_SCATTER_CAP", "0"))
         self.barrier_impl = os.environ.get("VC_SP_BARRIER", "own")         # own | torch
         self._flags, self._status, self._epoch = None, None, 0
+        self._status_host, self._status_event = None, None
 
     def side_stream(self):
         """High-priority stream for the q / k scatter launches that run under the next GEMM (ulysses_qkv_attention_overlapped)."""
@@ -119,11 +120,29 @@ class PeerExchange:
                                            ops._ptr(self._status), ops._stream()), "vc_peer_barrier")
             ops.launch_count += 1
 
-    def check_status(self):
-        """Raises if a barrier timed out (a peer never arrived).  Synchronises the current stream."""
+    def check_status(self, wait=False):
+        """Raises if a barrier of an EARLIER forward timed out (a peer never arrived).  Non-blocking by default: every call
+        queues an asynchronous copy of the status word to pinned host memory and looks at the copy queued by the previous
+        call once its event has completed, so the caller's launch queue is never drained; wait=True synchronises."""
         from . import _lib
-        if self._status is not None:
-            v = int(self._status.item())
+        if self._status is None:
+            return
+        if self._status_host is None:
+            self._status_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+            self._status_event = torch.cuda.Event()
+        elif wait or self._status_event.query():
+            if wait:
+                self._status_event.synchronize()
+            v = int(self._status_host[0])
+            if v != 0:
+                raise _lib.VCError(f"sequence-parallel barrier timed out waiting for rank {v & 0xff} (status {v & 0xffffffff:#x})")
+        else:
+            return   # the previous copy is still in flight: look again next time
+        self._status_host.copy_(self._status, non_blocking=True)
+        self._status_event.record()
+        if wait:
+            self._status_event.synchronize()
+            v = int(self._status_host[0])
             if v != 0:
                 raise _lib.VCError(f"sequence-parallel barrier timed out waiting for rank {v & 0xff} (status {v & 0xffffffff:#x})")
 
