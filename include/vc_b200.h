@@ -140,6 +140,13 @@ int vc_rmsnorm_rope_qkv_scatter(const void* qkv, long long ld, long long rows, l
  * *status = 0x80000000 | peer instead of hanging the GPU. */
 int vc_peer_barrier(void* const* flags, int rank, int n_peers, unsigned int epoch, int timeout_ms, void* status,
                     void* stream);
+/* Split form of vc_peer_barrier (same flag arrays, same epoch counter): vc_peer_signal publishes `epoch` to every peer once
+ * everything enqueued before it on the stream has completed; vc_peer_wait blocks the stream until every peer has published
+ * an epoch >= `epoch`.  Several signals may be outstanding; the host puts independent work between a signal and its wait
+ * (the interleaved backbone / GeoAdapter schedule under sequence parallelism) so that a late peer costs nothing.
+ * Replaces, like vc_peer_barrier, the synchronisation inside xfuser's all_to_all (wan_transformer3d.py:906-921). */
+int vc_peer_signal(void* const* flags, int rank, int n_peers, unsigned int epoch, void* stream);
+int vc_peer_wait(void* const* flags, int rank, int n_peers, unsigned int epoch, int timeout_ms, void* status, void* stream);
 int vc_gemm_bf16_scatter(const void* A, long long lda, const void* W, long long ldw, long long M, long long N,
                          long long K, const void* bias, long long rows_per_batch, long long pos_offset,
                          void* const* peer_recv, int n_peers, int heads_per_peer, int head_dim, long long l_total,

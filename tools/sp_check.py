@@ -15,7 +15,7 @@ def main():
     rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(lr)
     dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
-    cfg = dict(dim=1024, ffn_dim=2048, num_heads=8, num_layers=2, text_dim=256, geoada_in_dim=128)
+    cfg = dict(dim=1024, ffn_dim=2048, num_heads=8, num_layers=4, text_dim=256, geoada_in_dim=128)
     grid = (4, 32, 48)  # L = 1536, divisible by 8
     model = VerseCrafterWanTransformer3DModel(**cfg, device="cuda", dtype=torch.bfloat16, init=False).synthetic_init_(0)
     g = torch.Generator(device="cuda").manual_seed(5)
@@ -34,8 +34,11 @@ def main():
     singles = [model(*a).float() for _, a in cases]
     model.enable_multi_gpus_inference()
     all_ok = True
-    for mode in ("nccl", "fused"):  # NCCL all_to_all path, then the peer-memory path fused into the kernels
-        os.environ["VC_SP_MODE"] = mode
+    # NCCL all_to_all path, the peer-memory path fused into the kernels, then the same with the two-chain interleaved
+    # schedule and split signal / wait barriers (transformer._run_blocks_interleaved)
+    for mode in ("nccl", "fused", "fused+interleave"):
+        os.environ["VC_SP_MODE"] = mode.split("+")[0]
+        model.sp_interleave = "1" if mode.endswith("interleave") else "0"
         model._px, model._px_failed = None, False
         for (name, a), y1 in zip(cases, singles):
             yp = model(*a).float()
@@ -46,7 +49,9 @@ def main():
             used = "fused" if model._px is not None else "nccl"
             cos = float(torch.nn.functional.cosine_similarity(y1.flatten().double(), yp.flatten().double(), dim=0))
             rel = float((y1 - yp).norm() / y1.norm())
-            ok = cos > 0.9999 and rel < 1e-2 and torch.equal(yp, yp2) and used == mode
+            ok = cos > 0.9999 and rel < 1e-2 and torch.equal(yp, yp2) and used == mode.split("+")[0]
+            if mode.endswith("interleave"):
+                ok = ok and model._interleave_active() and torch.equal(yp, y1)
             flags = torch.tensor([1.0 if ok else 0.0], device="cuda")
             dist.all_reduce(flags, op=dist.ReduceOp.MIN)
             all_ok = all_ok and flags.item() == 1

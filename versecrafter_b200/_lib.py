@@ -26,6 +26,8 @@ SIGNATURES = {
     "vc_rmsnorm_rope_qkv_scatter": (_i, [_vp, _c_ll, _c_ll, _c_ll, _c_ll, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f,
                                          _vpp, _i, _i, _c_ll, _i, _vp]),
     "vc_peer_barrier": (_i, [_vpp, _i, _i, ctypes.c_uint, _i, _vp, _vp]),
+    "vc_peer_signal": (_i, [_vpp, _i, _i, ctypes.c_uint, _vp]),
+    "vc_peer_wait": (_i, [_vpp, _i, _i, ctypes.c_uint, _i, _vp, _vp]),
     "vc_gemm_bf16_scatter": (_i, [_vp, _c_ll, _vp, _c_ll, _c_ll, _c_ll, _c_ll, _vp, _c_ll, _c_ll, _vpp, _i, _i, _i, _c_ll, _i,
                                   _vp]),
     "vc_flash_attn_fwd_scatter": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _llp, _llp, _llp, _vpp, _i, _i, _llp, _f, _i,

@@ -14,17 +14,23 @@ struct FlagPtrs {
   unsigned int* p[8];
 };
 
+// kPhase: 3 = barrier (publish, then wait); 1 = publish only; 2 = wait only.  The split form lets the host put independent
+// work between "my remote stores are done" and "I need the peers' stores" (the interleaved two-chain schedule of
+// transformer._run_blocks_interleaved): a peer that is late by less than that work costs nothing.
+template <int kPhase>
 __global__ void __launch_bounds__(32, 1) peer_barrier_kernel(FlagPtrs flags, int rank, int n_peers, unsigned int epoch,
                                                              unsigned long long timeout_ns, unsigned int* status) {
   const int p = threadIdx.x;
   if (p >= n_peers) return;
   // an earlier barrier of this group timed out: the step is lost; publish the epoch (peers may still be waiting) but do not
   // spend another timeout in each of the remaining barriers of the forward
-  const bool failed = *reinterpret_cast<volatile unsigned int*>(status) != 0u;
+  const bool failed = (kPhase & 2) ? *reinterpret_cast<volatile unsigned int*>(status) != 0u : false;
   __threadfence_system();
-  if (p != rank) {
+  if ((kPhase & 1) && p != rank) {
     unsigned int* remote = flags.p[p] + rank;
     asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(remote), "r"(epoch) : "memory");
+  }
+  if ((kPhase & 2) && p != rank) {
     const unsigned int* mine = flags.p[rank] + p;
     unsigned long long t0;
     asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t0));
@@ -59,6 +65,32 @@ extern "C" int vc_peer_barrier(void* const* flags, int rank, int n_peers, unsign
   for (int i = 0; i < 8; ++i) fp.p[i] = (unsigned int*)(i < n_peers ? flags[i] : nullptr);
   for (int i = 0; i < n_peers; ++i) VC_CHECK_ARG(fp.p[i] && (uintptr_t)fp.p[i] % 4 == 0, "vc_peer_barrier: bad flag pointer %d", i);
   const unsigned long long ns = (unsigned long long)(timeout_ms > 0 ? timeout_ms : 5000) * 1000000ull;
-  peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(fp, rank, n_peers, epoch, ns, (unsigned int*)status);
+  peer_barrier_kernel<3><<<1, 32, 0, (cudaStream_t)stream>>>(fp, rank, n_peers, epoch, ns, (unsigned int*)status);
   VC_RETURN_LAUNCH_STATUS("vc_peer_barrier");
+}
+
+// Split form of vc_peer_barrier.  vc_peer_signal publishes `epoch` to every peer (everything enqueued before it on this
+// stream, remote stores included, has completed by then); vc_peer_wait blocks the stream until every peer has published an
+// epoch >= `epoch`.  Epochs come from ONE counter per group that every rank advances in the same order, so a flag slot
+// only grows and several signals may be outstanding.  vc_peer_barrier(e) == vc_peer_signal(e); vc_peer_wait(e).
+extern "C" int vc_peer_signal(void* const* flags, int rank, int n_peers, unsigned int epoch, void* stream) {
+  VC_CHECK_ARG(flags, "vc_peer_signal: null pointer");
+  VC_CHECK_ARG(n_peers >= 1 && n_peers <= 8 && rank >= 0 && rank < n_peers, "vc_peer_signal: bad rank %d of %d", rank, n_peers);
+  FlagPtrs fp;
+  for (int i = 0; i < 8; ++i) fp.p[i] = (unsigned int*)(i < n_peers ? flags[i] : nullptr);
+  for (int i = 0; i < n_peers; ++i) VC_CHECK_ARG(fp.p[i] && (uintptr_t)fp.p[i] % 4 == 0, "vc_peer_signal: bad flag pointer %d", i);
+  peer_barrier_kernel<1><<<1, 32, 0, (cudaStream_t)stream>>>(fp, rank, n_peers, epoch, 0ull, nullptr);
+  VC_RETURN_LAUNCH_STATUS("vc_peer_signal");
+}
+
+extern "C" int vc_peer_wait(void* const* flags, int rank, int n_peers, unsigned int epoch, int timeout_ms, void* status,
+                            void* stream) {
+  VC_CHECK_ARG(flags && status, "vc_peer_wait: null pointer");
+  VC_CHECK_ARG(n_peers >= 1 && n_peers <= 8 && rank >= 0 && rank < n_peers, "vc_peer_wait: bad rank %d of %d", rank, n_peers);
+  FlagPtrs fp;
+  for (int i = 0; i < 8; ++i) fp.p[i] = (unsigned int*)(i < n_peers ? flags[i] : nullptr);
+  for (int i = 0; i < n_peers; ++i) VC_CHECK_ARG(fp.p[i] && (uintptr_t)fp.p[i] % 4 == 0, "vc_peer_wait: bad flag pointer %d", i);
+  const unsigned long long ns = (unsigned long long)(timeout_ms > 0 ? timeout_ms : 5000) * 1000000ull;
+  peer_barrier_kernel<2><<<1, 32, 0, (cudaStream_t)stream>>>(fp, rank, n_peers, epoch, ns, (unsigned int*)status);
+  VC_RETURN_LAUNCH_STATUS("vc_peer_wait");
 }

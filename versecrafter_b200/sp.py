@@ -98,6 +98,17 @@ class PeerExchange:
             self.bufs[name] = ent
         return ent[0], ent[1]
 
+    def _ensure_flags(self):
+        from . import ops
+        if self._flags is None:
+            t, ptrs = self.buffer("barrier_flags", 64)        # 128 bytes: 8 u32 epoch slots (+ padding) per rank
+            t.zero_()
+            self._status = torch.zeros(1, dtype=torch.int32, device=self.device)
+            torch.cuda.current_stream().synchronize()
+            self.bufs["barrier_flags"][2].barrier(channel=0)   # everybody's slots are zero before the first epoch
+            torch.cuda.current_stream().synchronize()
+            self._flags = ops._ptr_array(ptrs)
+
     def barrier(self):
         """Stream-ordered barrier of the group.  Default: this library's epoch-flag kernel (vc_peer_barrier, one NVLink
         round trip, csrc/peer_sync.cu); VC_SP_BARRIER=torch uses torch symmetric memory's barrier."""
@@ -106,18 +117,37 @@ class PeerExchange:
             if self.barrier_impl == "torch":
                 next(iter(self.bufs.values()))[2].barrier(channel=0)
                 return
-            if self._flags is None:
-                t, ptrs = self.buffer("barrier_flags", 64)        # 128 bytes: 8 u32 epoch slots (+ padding) per rank
-                t.zero_()
-                self._status = torch.zeros(1, dtype=torch.int32, device=self.device)
-                torch.cuda.current_stream().synchronize()
-                self.bufs["barrier_flags"][2].barrier(channel=0)   # everybody's slots are zero before the first epoch
-                torch.cuda.current_stream().synchronize()
-                self._flags = ops._ptr_array(ptrs)
+            self._ensure_flags()
             self._epoch += 1
             lib = _lib.load()
             _lib.check(lib.vc_peer_barrier(self._flags, self.rank, self.P, self._epoch & 0xFFFFFFFF, 0,
                                            ops._ptr(self._status), ops._stream()), "vc_peer_barrier")
+            ops.launch_count += 1
+
+    def signal(self):
+        """First half of a split barrier: tells every peer that everything enqueued so far on this stream (remote stores
+        included) has completed.  Returns the epoch to hand to `wait`.  Every rank must call signal / wait / barrier in the
+        same order (one epoch counter).  With VC_SP_BARRIER=torch there is no split form: signal is a no-op and wait is the
+        full barrier."""
+        from . import _lib, ops
+        if self.barrier_impl == "torch":
+            return None
+        self._ensure_flags()
+        self._epoch += 1
+        with ops._timed("barrier", 0.0):
+            _lib.check(_lib.load().vc_peer_signal(self._flags, self.rank, self.P, self._epoch & 0xFFFFFFFF, ops._stream()),
+                       "vc_peer_signal")
+            ops.launch_count += 1
+        return self._epoch
+
+    def wait(self, epoch):
+        """Second half: the stream continues once every peer has signalled `epoch` (or a later one)."""
+        from . import _lib, ops
+        if epoch is None:
+            return self.barrier()
+        with ops._timed("barrier", 0.0):
+            _lib.check(_lib.load().vc_peer_wait(self._flags, self.rank, self.P, epoch & 0xFFFFFFFF, 0, ops._ptr(self._status),
+                                                ops._stream()), "vc_peer_wait")
             ops.launch_count += 1
 
     def check_status(self, wait=False):
@@ -182,6 +212,43 @@ def ulysses_attention_fused(px, qkv, B, Lp, H, d, gain_q, gain_k, rope, grid, ep
                            variant=variant)
     px.barrier()  # every peer's head slices of my tokens have landed; peers are done reading their qkv_recv
     return attn_t[:n_attn].view(B * Lp, D)
+
+
+def ulysses_fused_phases(px, qkv, B, Lp, H, d, gain_q, gain_k, rope, grid, eps, variant, k_true=None, tag=""):
+    """ulysses_attention_fused cut at its two barriers, each barrier split into signal (end of the producing phase) and
+    wait (start of the consuming phase), so that the caller can run another chain's kernels in between
+    (transformer._run_blocks_interleaved).  Returns three callables; the last returns the attention output [B*Lp, H*d].
+    `tag` selects a separate pair of symmetric buffers (two chains are in flight at once).  Same kernels, same arithmetic.
+    Buffer reuse is ordered as in the un-split form: a chain's next scatter into the peers' qkv_recv follows its wait on the
+    peers' post-attention signal; its next attention (writing the peers' attn_recv) follows its wait on the peers'
+    post-scatter signal, which the peers issue after their previous o-projection has read attn_recv."""
+    from . import ops
+    P, rank = px.P, px.rank
+    Hp, L, D = H // P, P * Lp, H * d
+    n_recv, n_attn = 3 * B * L * Hp * d, B * Lp * D
+    recv_t, recv_ptrs = px.buffer("qkv_recv" + tag, n_recv)
+    attn_t, attn_ptrs = px.buffer("attn_recv" + tag, n_attn)
+    ep = {}
+
+    def scatter():
+        ops.rmsnorm_rope_qkv_scatter(qkv, D, gain_q, gain_k, Lp, recv_ptrs, Hp, L, rope, grid, pos_offset=rank * Lp, eps=eps,
+                                     bulk=px.scatter_bulk)
+        ep[1] = px.signal()
+
+    def attention():
+        px.wait(ep[1])
+        r = recv_t[:n_recv].view(3, B, L, Hp, d)
+        head_off = rank * Hp * d * 2
+        Lk = L if k_true is None else min(k_true, L)
+        ops.flash_attn_scatter(r[0], r[1][:, :Lk], r[2][:, :Lk], [p + head_off for p in attn_ptrs], Lp, (Lp * D, D, d),
+                               variant=variant)
+        ep[2] = px.signal()
+
+    def gathered():
+        px.wait(ep[2])
+        return attn_t[:n_attn].view(B * Lp, D)
+
+    return scatter, attention, gathered
 
 
 def ulysses_qkv_attention_overlapped(px, h, wqkv, bqkv, qkv, B, Lp, H, d, gain_q, gain_k, rope, grid, eps, variant,

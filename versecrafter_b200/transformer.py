@@ -214,6 +214,12 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         # (sp.ulysses_qkv_attention_overlapped) — bit-identical, but measured no faster on 2 GPUs at c3: the remote stores
         # slow the GEMM they hide behind by as much as they cost alone (profiles/sp_overlap_ab_n2_r02.jsonl), so it is opt-in
         self.sp_overlap = os.environ.get("VC_SP_OVERLAP", "0") == "1"
+        # VC_SP_INTERLEAVE=1: under sequence parallelism the GeoAdapter chain (c) and the backbone chain (x) advance as two
+        # interleaved kernel sequences on the one stream, switching at the Ulysses exchange points, and every cross-GPU
+        # barrier is split into signal / wait with a phase of the OTHER chain in between (_run_blocks_interleaved): a peer
+        # that is late by less than that phase costs nothing.  Same kernels on the same data: bit-identical results.
+        # "force" runs the same schedule on one GPU (tests).
+        self.sp_interleave = os.environ.get("VC_SP_INTERLEAVE", "0")
         self.attn_variant = int(os.environ.get("VC_ATTN_VARIANT", "4"))
         # cross-attention (512 text keys): two-CTAs-per-SM short-key kernel with 64-key tiles and a double-buffered S (variant 7)
         self.xattn_variant = int(os.environ.get("VC_XATTN_VARIANT", "7"))
@@ -577,15 +583,19 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
                  rows_per_batch=Lp, residual=x2d, out=x2d)
         return self._block_tail(blk, x2d, m, ctx, st, h, attn)
 
-    def _block_tail(self, blk, x2d, m, ctx, st, h, attn):
+    def _block_tail(self, blk, x2d, m, ctx, st, h, attn, tag=""):
         """cross-attention + FFN halves of the block (token-local under sequence parallelism)."""
+        self._block_cross(blk, x2d, ctx, st, h, attn, tag)
+        return self._block_ffn(blk, x2d, m, st, h, tag)
+
+    def _block_cross(self, blk, x2d, ctx, st, h, attn, tag=""):
         B, Lp, D, H = st.B, st.Lp, self.dim, self.num_heads
         rows = B * Lp
         pk = blk.ensure_packed()
         ca = blk.cross_attn
         # cross-attention
         ops.ln_affine(x2d, blk.norm3.weight, blk.norm3.bias, eps=self.eps, out=h)
-        qc = ops.gemm(h, ca.q.weight, ca.q.bias, out=self._buf("qc", (rows, D)))
+        qc = ops.gemm(h, ca.q.weight, ca.q.bias, out=self._buf("qc" + tag, (rows, D)))
         ops.rmsnorm_rope_(qc, D, 1, ca.norm_q.weight, None, Lp, eps=self.eps)
         T = ctx.shape[0] // B
         sc = st.step_cache
@@ -599,7 +609,7 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
             kv = hit[1]
         else:
             dst = torch.empty((B * T, 2 * D), dtype=torch.bfloat16, device=self.device) if sc is not None \
-                else self._buf("kv", (B * T, 2 * D))
+                else self._buf("kv" + tag, (B * T, 2 * D))
             kv = ops.gemm(ctx, pk["wkv"], pk["bkv"], out=dst)
             ops.rmsnorm_rope_(kv, D, 1, ca.norm_k.weight, None, T, eps=self.eps)
             if sc is not None:
@@ -607,14 +617,67 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         ops.flash_attn(qc.view(B, Lp, H, self.d), kv[:, :D].view(B, T, H, self.d), kv[:, D:].view(B, T, H, self.d),
                        out=attn.view(B, Lp, H, self.d), variant=self.xattn_variant)
         ops.gemm(attn, ca.o.weight, ca.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_RES, residual=x2d, out=x2d)
-        # FFN half
+
+    def _block_ffn(self, blk, x2d, m, st, h, tag=""):
+        Lp = st.Lp
+        rows = st.B * Lp
         ops.ln_modulate(x2d, m[:, 3], m[:, 4], Lp, eps=self.eps, out=h)
         f1, f2 = blk.ffn[0], blk.ffn[2]
         hid = ops.gemm(h, f1.weight, f1.bias, epilogue=ops.EPI_BIAS | ops.EPI_GELU,
-                       out=self._buf("ffn", (rows, self.ffn_dim)))
+                       out=self._buf("ffn" + tag, (rows, self.ffn_dim)))
         ops.gemm(hid, f2.weight, f2.bias, epilogue=ops.EPI_BIAS | ops.EPI_GATE | ops.EPI_RES, gate=m[:, 5],
                  rows_per_batch=Lp, residual=x2d, out=x2d)
         return x2d
+
+    def _block_phases(self, blk, x2d, m, ctx, st, tag=""):
+        """The block of `_block` as four callables cut where the interleaved schedule switches chains:
+          [0] LN+modulate, QKV GEMM, RMSNorm+RoPE + head scatter to the peers, SIGNAL
+          [1] WAIT, self-attention on the local heads (+ output scatter to the token owners), SIGNAL
+          [2] WAIT, o projection (+gate +residual), cross-attention half
+          [3] FFN half
+        `tag` names this chain's workspace and exchange buffers (two chains are in flight).  Sequence-parallel ranks use the
+        fused exchange (sp.ulysses_fused_phases); on one GPU (tests: VC_SP_INTERLEAVE=force) the phases are the plain kernels."""
+        B, Lp, D, H = st.B, st.Lp, self.dim, self.num_heads
+        rows = B * Lp
+        pk = blk.ensure_packed()
+        sa = blk.self_attn
+        h = self._buf("h" + tag, (rows, D))
+        attn = self._buf("attn" + tag, (rows, D))
+        box = {}
+        fused = self.sp_world_size > 1
+
+        def p_qkv():
+            ops.ln_modulate(x2d, m[:, 0], m[:, 1], Lp, eps=self.eps, out=h)
+            qkv = ops.gemm(h, pk["wqkv"], pk["bqkv"], out=self._buf("qkv" + tag, (rows, 3 * D)))
+            if fused:
+                box["ph"] = sp.ulysses_fused_phases(self._peer_exchange(), qkv, B, Lp, H, self.d, sa.norm_q.weight,
+                                                    sa.norm_k.weight, st.rope, st.grid, self.eps, max(self.attn_variant, 2),
+                                                    k_true=st.l_true, tag=tag)
+                box["ph"][0]()
+            else:
+                ops.rmsnorm_rope_(qkv, D, 2, sa.norm_q.weight, sa.norm_k.weight, Lp, eps=self.eps, rope=st.rope, grid=st.grid,
+                                  pos_offset=0)
+                box["qkv"] = qkv
+
+        def p_attn():
+            if fused:
+                box["ph"][1]()
+            else:
+                q4, k4, v4 = (box["qkv"][:, i * D:(i + 1) * D].view(B, Lp, H, self.d) for i in range(3))
+                if st.k_len < Lp:
+                    k4, v4 = k4[:, :st.k_len], v4[:, :st.k_len]
+                ops.flash_attn(q4, k4, v4, out=attn.view(B, Lp, H, self.d), variant=self.attn_variant)
+
+        def p_o_cross():
+            a = box["ph"][2]() if fused else attn
+            ops.gemm(a, sa.o.weight, sa.o.bias, epilogue=ops.EPI_BIAS | ops.EPI_GATE | ops.EPI_RES, gate=m[:, 2],
+                     rows_per_batch=Lp, residual=x2d, out=x2d)
+            self._block_cross(blk, x2d, ctx, st, h, attn, tag)
+
+        def p_ffn():
+            self._block_ffn(blk, x2d, m, st, h, tag)
+
+        return [p_qkv, p_attn, p_o_cross, p_ffn]
 
     def _geo_block(self, j, c2d, x2d, e0, ctx, st):
         """GeoAdapter block j on the control stream c (VerseCrafterWanAttentionBlock.forward :112-125)."""
@@ -659,6 +722,86 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
                              residual=x2d, scale=float(scale), out=x2d)
                 else:  # geo block j ran earlier for a smaller layer index and c has moved on
                     raise VCError("internal: hint ordering")
+            if self.record is not None:
+                self.record[f"blk_out.{i}"] = x2d.view(st.B, st.Lp, -1).clone()
+        return x2d
+
+    def _interleave_active(self):
+        if self.sp_interleave == "force":
+            ok = self.sp_world_size == 1
+        else:
+            ok = self.sp_interleave == "1" and self.sp_world_size > 1 and self._peer_exchange() is not None \
+                and not self.sp_overlap
+        gl = self.geoada_layers
+        return ok and self.d == 128 and all(a < b for a, b in zip(gl, gl[1:]))   # hints consumed in block order
+
+    def _run_blocks_interleaved(self, x2d, c2d, e0, ctx, st, scale):
+        """Same blocks, same kernels, same results as `_run_blocks`; different ORDER on the stream.  The control chain
+        (GeoAdapter block j+1 only needs block j) runs ahead of its consumer and is cut into the four phases of
+        `_block_phases`; a backbone layer is issued as
+            X[0] (… scatter, SIGNAL) · one c phase · X[1] (WAIT, attention, SIGNAL) · one c phase · X[2] (WAIT, …) · X[3]
+        so every WAIT of either chain has at least one phase of the other chain (>= 1 ms at c3 on 8 GPUs) between it and
+        its SIGNAL: lock-step waiting for whichever GPU is momentarily slowest (120 barriers per step) is
+        absorbed instead of added up.  Constraints kept: c phase [2] of block j+1 updates c in place, so it runs after
+        `after_proj(c_j)` has read c (hint j consumed after layer geoada_layers[j], :144-148); block j is drained before that."""
+        n_geo = len(self.geoada_blocks)
+        queue, state = [], dict(next_geo=0, done=-1, consumed=-1)
+
+        def start_geo(j):
+            blk = self.geoada_blocks[j]
+            ph = self._block_phases(blk, c2d, st.m_all[self.num_layers + j], ctx, st, tag=".c")
+
+            def first():
+                if j == 0:  # c = before_proj(c_emb) + x0; x is untouched until the first o projection of layer 0
+                    bp = blk.before_proj
+                    ops.gemm(st.c_emb, bp.weight, bp.bias, epilogue=ops.EPI_BIAS | ops.EPI_RES, residual=x2d, out=c2d)
+                if self.record is not None:
+                    self.record[f"geo_in.{j}"] = c2d.view(st.B, st.Lp, -1).clone()
+                ph[0]()
+
+            def last():
+                ph[3]()
+                if self.record is not None:
+                    self.record[f"geo_out.{j}"] = c2d.view(st.B, st.Lp, -1).clone()
+
+            queue.extend([(j, 0, first), (j, 1, ph[1]), (j, 2, ph[2]), (j, 3, last)])
+
+        def c_step():
+            if not queue and state["next_geo"] < n_geo:
+                start_geo(state["next_geo"])
+                state["next_geo"] += 1
+            if not queue:
+                return False
+            j, k, fn = queue[0]
+            if k == 2 and state["consumed"] < j - 1:   # after_proj(c_{j-1}) has not read c yet
+                return False
+            queue.pop(0)
+            fn()
+            if k == 3:
+                state["done"] = j
+            return True
+
+        for i, blk in enumerate(self.blocks):
+            j = self.geoada_layers_mapping.get(i)
+            if self.record is not None:
+                self.record[f"blk_in.{i}"] = x2d.view(st.B, st.Lp, -1).clone()
+            xp = self._block_phases(blk, x2d, st.m_all[i], ctx, st)
+            xp[0]()
+            c_step()
+            xp[1]()
+            c_step()
+            xp[2]()
+            xp[3]()
+            if j is not None:
+                while state["done"] < j:
+                    if not c_step():
+                        raise VCError("internal: control chain cannot advance")
+                ap = self.geoada_blocks[j].after_proj
+                if self.record is not None:
+                    self.record[f"hint.{j}"] = ops.gemm(c2d, ap.weight, ap.bias).view(st.B, st.Lp, -1)
+                ops.gemm(c2d, ap.weight, ap.bias, epilogue=ops.EPI_BIAS | ops.EPI_SCALE | ops.EPI_RES,
+                         residual=x2d, scale=float(scale), out=x2d)
+                state["consumed"] = j
             if self.record is not None:
                 self.record[f"blk_out.{i}"] = x2d.view(st.B, st.Lp, -1).clone()
         return x2d
@@ -729,10 +872,13 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
             should_calc = self._teacache_decide(e0, t, cond_flag)
         if should_calc:
             c2d = self._buf("c", (B * Lp, D))
-            st.c_emb = self._buf("attn", (B * Lp, D))   # free until the first attention call; read by before_proj only
+            interleave = self._interleave_active()
+            # plain schedule: the idle attention workspace (free until the first attention call; read by before_proj only);
+            # interleaved: before_proj runs inside layer 0, so the embedded control tokens get a buffer of their own
+            st.c_emb = self._buf("c_emb" if interleave else "attn", (B * Lp, D))
             self._patch_embed([u for u in geoada_context], self.geoada_patch_embedding, st.c_emb, seq_len_p, Lp, "ge_a")
             ori = x2d.clone() if self.teacache is not None else None
-            self._run_blocks(x2d, c2d, e0, ctx, st, scale)
+            (self._run_blocks_interleaved if interleave else self._run_blocks)(x2d, c2d, e0, ctx, st, scale)
             if self.teacache is not None:
                 res = x2d - ori
                 res = res.cpu() if self.teacache.offload else res
