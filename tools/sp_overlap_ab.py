@@ -29,6 +29,7 @@ VARIANTS = [
     ("full_bulk", dict(overlap=True, mode="full", bulk=True, cap=0)),
     ("full_bulk_cap1", dict(overlap=True, mode="full", bulk=True, cap=1)),
     ("full_bulk_cap2", dict(overlap=True, mode="full", bulk=True, cap=2)),
+    ("interleave", dict(overlap=False, bulk=False, cap=0, interleave=True)),   # two-chain schedule, split signal / wait barriers
     ("one_scatter", dict(overlap=False, bulk=False, cap=0)),   # again: drift of the box over the run
     ("one_scatter_torch_barrier", dict(overlap=False, bulk=False, cap=0, barrier="torch")),
 ]
@@ -40,6 +41,7 @@ def main():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--only", default="")
+    ap.add_argument("--seq", default="", help="comma-separated variant names, run in this order (repeats allowed)")
     args = ap.parse_args()
     rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(lr)
@@ -59,9 +61,14 @@ def main():
 
     first = None
     only = [s for s in args.only.split(",") if s]
-    for name, v in VARIANTS:
+    todo = VARIANTS
+    if args.seq:
+        table = dict(VARIANTS)
+        todo = [(n, table[n]) for n in args.seq.split(",")]
+    for name, v in todo:
         if only and name not in only:
             continue
+        model.sp_interleave = "1" if v.get("interleave") else "0"
         px = model._peer_exchange()
         assert px is not None, "symmetric memory unavailable"
         model.sp_overlap = v["overlap"]
