@@ -221,8 +221,9 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         # "force" runs the same schedule on one GPU (tests).
         self.sp_interleave = os.environ.get("VC_SP_INTERLEAVE", "0")
         self.attn_variant = int(os.environ.get("VC_ATTN_VARIANT", "4"))
-        # cross-attention (512 text keys): two-CTAs-per-SM short-key kernel with 64-key tiles and a double-buffered S (variant 7)
-        self.xattn_variant = int(os.environ.get("VC_XATTN_VARIANT", "7"))
+        # cross-attention (512 text keys): persistent two-CTAs-per-SM short-key kernel, 64-key tiles, double-buffered S (variant 9;
+        # 0.90 ms per launch in the c3 step vs 1.22 ms for the one-tile-per-CTA variant 7, profiles/bench_c3_r02k_x{7,9}_*.json)
+        self.xattn_variant = int(os.environ.get("VC_XATTN_VARIANT", "9"))
         self.implicit_patch_embed = os.environ.get("VC_PATCH_EMBED", "implicit") != "explicit"
         self._ws = {}
         self._rope_cache = {}
