@@ -969,7 +969,12 @@ int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_p
     VC_CHECK_ARG(rcb == 0, "vc_rmsnorm_rope_qk: unsupported D=%d", D);
     VC_RETURN_LAUNCH_STATUS("vc_rmsnorm_rope_qk");
   }
-  if (D > 1024 && (!apply_rope || (ROW_NT * 8) % (2 * (nf + nh + nw)) == 0)) {
+  // Self-attention q|k with RoPE is the case vc_rmsnorm_rope_qkv_scatter mirrors under sequence parallelism; that kernel is
+  // block-per-row for every D, so this one is too (same fp32 summation order => the sequence-parallel forward is bit-identical
+  // to the single-GPU one also at D <= 1024, where the warp-per-row kernel would otherwise round the sum of squares differently
+  // in about one row per million: tools/sp_diag.py).
+  const bool mirrored = n_mats == 2 && apply_rope;
+  if ((D > 1024 || mirrored) && (!apply_rope || (ROW_NT * 8) % (2 * (nf + nh + nw)) == 0)) {
     int rcb = dispatch_vpt(D, [&](auto vpt) {
       constexpr int V = decltype(vpt)::value;
       rmsnorm_rope_block_kernel<V><<<grid_for_block_rows(rows), ROW_NT, 0, (cudaStream_t)stream>>>(
