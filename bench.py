@@ -60,7 +60,7 @@ def work_per_step(cfg, L, B, T=512):
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons during the timed region."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.limit")
 
     def __init__(self, index):
         self.index, self.rows, self.proc = index, [], None
@@ -82,18 +82,25 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.25)
         self.proc.terminate()
-        sm, mx, reasons = [], None, set()
+        sm, mx, reasons, pw, plim = [], None, set(), [], None
         for r in self.rows:
             try:
                 sm.append(float(r[0])); mx = float(r[1])
             except Exception:  # noqa: BLE001
                 continue
+            try:
+                pw.append(float(r[2])); plim = float(r[7])
+            except Exception:  # noqa: BLE001
+                pass
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         sm.sort()
+        pw.sort()
+        # power_w_median / power_limit_w: the step runs AT the board power limit (reason sw_power_cap), which is why
+        # schedule changes that remove idle time do not shorten it
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "power_w_median": pw[len(pw) // 2] if pw else None, "power_limit_w": plim}
 
 
 def make_inputs(cfg, grid, B=2):
@@ -334,6 +341,7 @@ def run_gpu_arm(args):
         dist.all_reduce(stats, op=dist.ReduceOp.MIN)
         sp_parity = {"cosine": float(stats[0]), "rel_l2": -float(stats[1]), "bit_identical": bool(stats[2] == 1.0),
                      "mode": "fused" if model._px is not None else "nccl",
+                     "schedule": "interleaved (two chains, split signal/wait barriers)" if model._interleave_active() else "plain",
                      "what": "gathered SP forward vs the rank-local P=1 forward of the same inputs, worst over ranks"}
         del y_sp, y_one
         model.release_workspace()       # the P=1 workspace is not part of the SP step
