@@ -52,6 +52,11 @@ def test_argument_errors_do_not_need_a_gpu(lib):
     rc = lib.vc_ln_modulate(ctypes.c_void_p(16), 12, ctypes.c_void_p(16), 12, ctypes.c_void_p(16), ctypes.c_void_p(16), 0, 4, 4,
                             12, 1e-6, 0, None)
     assert rc < 0 and b"multiple of 8" in lib.vc_last_error()
+    # split barrier: rank outside the group, null flag table
+    flags = (ctypes.c_void_p * 8)(*[4096] * 8)
+    assert lib.vc_peer_signal(flags, 9, 8, 1, None) < 0 and b"bad rank" in lib.vc_last_error()
+    assert lib.vc_peer_wait(None, 0, 2, 1, 0, ctypes.c_void_p(64), None) < 0 and b"null" in lib.vc_last_error()
+    assert lib.vc_peer_wait(flags, 0, 9, 1, 0, ctypes.c_void_p(64), None) < 0 and b"bad rank" in lib.vc_last_error()
 
 
 def test_sass_is_blackwell_native():

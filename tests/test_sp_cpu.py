@@ -80,3 +80,61 @@ def test_bench_work_formula_matches_survey():
     cfg, grid, _ = bench.CONFIGS["c3"]
     gemm, attn = bench.work_per_step(cfg, 32760, 2)
     assert abs(gemm / 1e15 - 2.429) < 0.01 and abs(attn / 1e15 - 2.679) < 0.01
+
+
+@pytest.mark.parametrize("num_layers,geo_layers", [(8, None), (6, [0, 1, 4]), (5, [0, 3])])
+def test_interleaved_schedule_order(monkeypatch, num_layers, geo_layers):
+    """Host logic of transformer._run_blocks_interleaved (no GPU: the phases and the GEMM are replaced by recorders).
+    Checks the order it enqueues: each chain's phases in order; phase [2] of GeoAdapter block j+1 (which updates c in
+    place) after `after_proj(c_j)` has read c; hint j consumed right after backbone layer geoada_layers[j], with block j
+    complete; a backbone WAIT ([1], [2]) is preceded by a control phase whenever the control chain still has one that may run."""
+    from types import SimpleNamespace
+    from versecrafter_b200 import ops, transformer
+    cfg = dict(dim=128, ffn_dim=256, num_heads=1, num_layers=num_layers, text_dim=32, geoada_in_dim=128)
+    if geo_layers is not None:
+        cfg["geoada_layers"] = geo_layers
+    model = transformer.VerseCrafterWanTransformer3DModel(**cfg, device="cpu", dtype=torch.bfloat16, init=False)
+    log = []
+    blocks = {id(b): ("x", i) for i, b in enumerate(model.blocks)}
+    blocks.update({id(b): ("c", j) for j, b in enumerate(model.geoada_blocks)})
+
+    def fake_phases(blk, x2d, m, ctx, st, tag=""):
+        chain, idx = blocks[id(blk)]
+        assert tag == ("" if chain == "x" else ".c")
+        return [lambda k=k: log.append((chain, idx, k)) for k in range(4)]
+
+    def fake_gemm(a, w, b=None, **kw):
+        owner = next(("before", j) if (hasattr(g, "before_proj") and w is g.before_proj.weight) else ("after", j)
+                     for j, g in enumerate(model.geoada_blocks)
+                     if (hasattr(g, "before_proj") and w is g.before_proj.weight) or w is g.after_proj.weight)
+        log.append(owner + (None,))
+        return a
+
+    monkeypatch.setattr(model, "_block_phases", fake_phases)
+    monkeypatch.setattr(ops, "gemm", fake_gemm)
+    n_geo = len(model.geoada_blocks)
+    st = SimpleNamespace(B=1, Lp=4, m_all=[None] * (num_layers + n_geo), c_emb=torch.zeros(4, 128))
+    x2d, c2d = torch.zeros(4, 128), torch.zeros(4, 128)
+    model._run_blocks_interleaved(x2d, c2d, None, None, st, 1.0)
+
+    pos = {e: n for n, e in enumerate(log)}
+    assert len(pos) == len(log)                                            # nothing enqueued twice
+    for chain, n in (("x", num_layers), ("c", n_geo)):
+        seq = [e for e in log if e[0] == chain]
+        assert seq == [(chain, i, k) for i in range(n) for k in range(4)]   # every phase once, in chain order
+    layers = model.geoada_layers
+    assert pos[("before", 0, None)] < pos[("c", 0, 0)] and pos[("before", 0, None)] < pos[("x", 0, 2)]   # reads x0
+    for j in range(n_geo):
+        a = pos[("after", j, None)]
+        assert pos[("c", j, 3)] < a and pos[("x", layers[j], 3)] < a        # block j and its layer are complete
+        if layers[j] + 1 < num_layers:
+            assert a < pos[("x", layers[j] + 1, 0)]                         # the hint is in x before the next layer reads it
+        if j + 1 < n_geo:
+            assert a < pos[("c", j + 1, 2)]                                 # c_j read before block j+1 overwrites c
+    # slack: between a backbone SIGNAL (end of [0] / [1]) and its WAIT (start of [1] / [2]) sits a control phase, as long
+    # as the control chain has one whose constraints allow it
+    covered = sum(1 for i in range(num_layers) for k in (0, 1) if log[pos[("x", i, k)] + 1][0] == "c")
+    if geo_layers is None:   # every second layer: all control phases sit in such a slot except the two drained at the end of
+        assert covered == 4 * n_geo - 3   # layer 0 (hint 0 is due there); block 0's first slot starts with before_proj
+    else:
+        assert covered >= n_geo
