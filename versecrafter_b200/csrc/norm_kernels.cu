@@ -231,22 +231,6 @@ __device__ __forceinline__ float block_sum(float v, float* red) {  // red: ROW_N
 __device__ __forceinline__ __nv_bfloat162 as_bf162(uint32_t u) { return *reinterpret_cast<__nv_bfloat162*>(&u); }
 __device__ __forceinline__ uint32_t as_u32(__nv_bfloat162 v) { return *reinterpret_cast<uint32_t*>(&v); }
 __device__ __forceinline__ float2 up2(uint32_t u) { return vc::unpack_bf16x2(u); }
-__device__ __forceinline__ float vec_sum(const uint4& u) {
-  const float2 a = up2(u.x), b = up2(u.y), c = up2(u.z), d = up2(u.w);
-  return ((a.x + a.y) + (b.x + b.y)) + ((c.x + c.y) + (d.x + d.y));
-}
-__device__ __forceinline__ float vec_sumsq(const uint4& u, float mean, float ss) {
-  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const float2 f = up2(w[q]);
-    const float d0 = f.x - mean, d1 = f.y - mean;
-    ss = fmaf(d0, d0, ss);
-    ss = fmaf(d1, d1, ss);
-  }
-  return ss;
-}
-
 __device__ __forceinline__ float vec_sumsq0(const uint4& u, float ss) {
   const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
@@ -272,6 +256,89 @@ __device__ __forceinline__ uint4 rms_rope_vec(const uint4& x, __nv_bfloat162 r2,
     }
   }
   return make_uint4(ow[0], ow[1], ow[2], ow[3]);
+}
+
+
+// Packed fp32x2 arithmetic (sm_100 FADD2 / FMUL2 / FFMA2: one issue slot for two fp32 lanes).  Per-lane results are those of
+// the scalar instructions (round-to-nearest, ftz as everywhere in this file), so only the ORDER of a reduction can change bits.
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+  float2 d;
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+      "add.rn.ftz.f32x2 rd, ra, rb;\n\tmov.b64 {%0, %1}, rd;\n\t}\n"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return d;
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+  float2 d;
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+      "mul.rn.ftz.f32x2 rd, ra, rb;\n\tmov.b64 {%0, %1}, rd;\n\t}\n"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return d;
+}
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+  float2 d;
+  asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rc, {%6, %7};\n\t"
+      "fma.rn.ftz.f32x2 rd, ra, rb, rc;\n\tmov.b64 {%0, %1}, rd;\n\t}\n"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+  return d;
+}
+
+// LayerNorm of one row held as VPT 16-byte vectors per thread (ROW_NT threads), shared by the register and the ring kernel.
+// Round 2: the row is unpacked to fp32 pairs ONCE and all three passes (sum, centred sum of squares, normalise) run on packed
+// fp32x2 instructions: ~260 instead of ~430 issue slots per thread and 10 KB row — at the 1.4 GHz the power cap leaves these
+// kernels inside a step they are issue-bound, not HBM-bound (ncu: issue-active 62 % at 1.96 GHz).  Statistics are summed in two
+// (even / odd pair) packed accumulators.  Rounding points of the output as before (mode 0 / 1, see the kernels below).
+template <int VPT>
+__device__ __forceinline__ void ln_row(const uint4 (&raw)[VPT], const uint4 (&sc)[VPT], const uint4 (&sh)[VPT], int nvec,
+                                       float inv_d, float eps, int mode, float* red_a, float* red_b, uint4* orow) {
+  float2 xf[VPT * 4];
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    xf[i * 4 + 0] = up2(raw[i].x); xf[i * 4 + 1] = up2(raw[i].y);
+    xf[i * 4 + 2] = up2(raw[i].z); xf[i * 4 + 3] = up2(raw[i].w);
+  }
+  float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < VPT * 4; k += 2) {
+    a0 = add2(a0, xf[k]);
+    a1 = add2(a1, xf[k + 1]);
+  }
+  const float mean = block_sum((a0.x + a0.y) + (a1.x + a1.y), red_a) * inv_d;
+  const float2 nm = make_float2(-mean, -mean);
+  a0 = make_float2(0.f, 0.f);
+  a1 = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    if (threadIdx.x + ROW_NT * i < nvec) {   // masked vectors are zeros: they must not add mean^2
+      const float2 d0 = add2(xf[i * 4 + 0], nm), d1 = add2(xf[i * 4 + 1], nm);
+      const float2 d2 = add2(xf[i * 4 + 2], nm), d3 = add2(xf[i * 4 + 3], nm);
+      a0 = fma2(d0, d0, a0); a1 = fma2(d1, d1, a1);
+      a0 = fma2(d2, d2, a0); a1 = fma2(d3, d3, a1);
+    }
+  }
+  const float rstd = rsqrtf(block_sum((a0.x + a0.y) + (a1.x + a1.y), red_b) * inv_d + eps);
+  const float2 r2 = make_float2(rstd, rstd);
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int v = threadIdx.x + ROW_NT * i;
+    if (v < nvec) {
+      const uint32_t cw[4] = {sc[i].x, sc[i].y, sc[i].z, sc[i].w};
+      const uint32_t aw[4] = {sh[i].x, sh[i].y, sh[i].z, sh[i].w};
+      uint32_t ow[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float2 l = mul2(add2(xf[i * 4 + q], nm), r2);   // (x - mean) * rstd, one rounding each as in the scalar form
+        if (mode == 0) {
+          // bf(bf(bf(ln) * bf(1 + scale)) + shift)
+          ow[q] = as_u32(__hadd2_rn(__hmul2_rn(__floats2bfloat162_rn(l.x, l.y), as_bf162(cw[q])), as_bf162(aw[q])));
+        } else {
+          const float2 o = fma2(l, up2(cw[q]), up2(aw[q]));
+          ow[q] = vc::pack_bf16x2(o.x, o.y);
+        }
+      }
+      st_stream(orow + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
+    }
+  }
 }
 
 template <int VPT>
@@ -316,40 +383,7 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 2) ln_modulate_block_ke
         }
       }
     }
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < VPT; ++i) s += vec_sum(raw[i]);
-    const float mean = block_sum(s, red_a) * inv_d;
-    float ss = 0.f;
-#pragma unroll
-    for (int i = 0; i < VPT; ++i) {
-      if (threadIdx.x + ROW_NT * i < nvec) ss = vec_sumsq(raw[i], mean, ss);
-    }
-    const float rstd = rsqrtf(block_sum(ss, red_b) * inv_d + eps);
-    uint4* orow = reinterpret_cast<uint4*>(out + row * ldo);
-#pragma unroll
-    for (int i = 0; i < VPT; ++i) {
-      const int v = threadIdx.x + ROW_NT * i;
-      if (v < nvec) {
-        const uint32_t xw[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
-        const uint32_t cw[4] = {sc[i].x, sc[i].y, sc[i].z, sc[i].w};
-        const uint32_t aw[4] = {sh[i].x, sh[i].y, sh[i].z, sh[i].w};
-        uint32_t ow[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float2 f = up2(xw[q]);
-          const float l0 = (f.x - mean) * rstd, l1 = (f.y - mean) * rstd;
-          if (mode == 0) {
-            // bf(bf(bf(ln) * bf(1 + scale)) + shift)
-            ow[q] = as_u32(__hadd2_rn(__hmul2_rn(__floats2bfloat162_rn(l0, l1), as_bf162(cw[q])), as_bf162(aw[q])));
-          } else {
-            const float2 g = up2(cw[q]), bb = up2(aw[q]);
-            ow[q] = vc::pack_bf16x2(fmaf(l0, g.x, bb.x), fmaf(l1, g.y, bb.y));
-          }
-        }
-        st_stream(orow + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
-      }
-    }
+    ln_row<VPT>(raw, sc, sh, nvec, inv_d, eps, mode, red_a, red_b, reinterpret_cast<uint4*>(out + row * ldo));
   }
 }
 
@@ -502,39 +536,7 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 2) ln_modulate_ring_ker
       const int v = threadIdx.x + ROW_NT * i;
       raw[i] = (v < nvec) ? xr[v] : make_uint4(0, 0, 0, 0);
     }
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < VPT; ++i) s += vec_sum(raw[i]);
-    const float mean = block_sum(s, red_a) * inv_d;
-    float ss = 0.f;
-#pragma unroll
-    for (int i = 0; i < VPT; ++i) {
-      if (threadIdx.x + ROW_NT * i < nvec) ss = vec_sumsq(raw[i], mean, ss);
-    }
-    const float rstd = rsqrtf(block_sum(ss, red_b) * inv_d + eps);
-    uint4* orow = reinterpret_cast<uint4*>(out + row * ldo);
-#pragma unroll
-    for (int i = 0; i < VPT; ++i) {
-      const int v = threadIdx.x + ROW_NT * i;
-      if (v < nvec) {
-        const uint32_t xw[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
-        const uint32_t cw[4] = {sc[i].x, sc[i].y, sc[i].z, sc[i].w};
-        const uint32_t aw[4] = {sh[i].x, sh[i].y, sh[i].z, sh[i].w};
-        uint32_t ow[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float2 f = up2(xw[q]);
-          const float l0 = (f.x - mean) * rstd, l1 = (f.y - mean) * rstd;
-          if (mode == 0) {
-            ow[q] = as_u32(__hadd2_rn(__hmul2_rn(__floats2bfloat162_rn(l0, l1), as_bf162(cw[q])), as_bf162(aw[q])));
-          } else {
-            const float2 g = up2(cw[q]), bb = up2(aw[q]);
-            ow[q] = vc::pack_bf16x2(fmaf(l0, g.x, bb.x), fmaf(l1, g.y, bb.y));
-          }
-        }
-        st_stream(orow + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
-      }
-    }
+    ln_row<VPT>(raw, sc, sh, nvec, inv_d, eps, mode, red_a, red_b, reinterpret_cast<uint4*>(out + row * ldo));
   }
 }
 
