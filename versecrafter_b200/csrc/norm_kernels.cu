@@ -214,6 +214,23 @@ __global__ void __launch_bounds__(256) rmsnorm_rope_kernel(__nv_bfloat16* __rest
 // ----------------------------------------------------------------------------------------------------
 constexpr int ROW_NT = 128;
 
+// Row -> (batch, position) -> (f, h, w) in 32-bit unsigned arithmetic: rows, positions and the grid volume are < 2^31 (checked by
+// the launchers), and nvcc's 64-bit division costs ~5x the issue slots of the 32-bit one — with five of them per row these
+// integer sequences were ~15 % of an issue-bound row kernel.
+__device__ __forceinline__ unsigned row_batch(long long row, long long rows_per_batch, unsigned& in_batch) {
+  const unsigned r = (unsigned)row, n = (unsigned)rows_per_batch;
+  const unsigned b = r / n;
+  in_batch = r - b * n;
+  return b;
+}
+__device__ __forceinline__ void split_pos(unsigned pos, int Hg, int Wg, int& pf, int& ph, int& pw) {
+  const unsigned t = pos / (unsigned)Wg;
+  pw = (int)(pos - t * (unsigned)Wg);
+  const unsigned f = t / (unsigned)Hg;
+  ph = (int)(t - f * (unsigned)Hg);
+  pf = (int)f;
+}
+
 __device__ __forceinline__ float block_sum(float v, float* red) {  // red: ROW_NT/32 floats, reused only after a sync
   v = warp_sum(v);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
@@ -231,34 +248,6 @@ __device__ __forceinline__ float block_sum(float v, float* red) {  // red: ROW_N
 __device__ __forceinline__ __nv_bfloat162 as_bf162(uint32_t u) { return *reinterpret_cast<__nv_bfloat162*>(&u); }
 __device__ __forceinline__ uint32_t as_u32(__nv_bfloat162 v) { return *reinterpret_cast<uint32_t*>(&v); }
 __device__ __forceinline__ float2 up2(uint32_t u) { return vc::unpack_bf16x2(u); }
-__device__ __forceinline__ float vec_sumsq0(const uint4& u, float ss) {
-  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const float2 f = up2(w[q]);
-    ss = fmaf(f.x, f.x, ss);
-    ss = fmaf(f.y, f.y, ss);
-  }
-  return ss;
-}
-// one 16-byte vector of q or k: bf(bf(x * r) * g), then the adjacent-pair rotation in fp32 (one rounding at the pack)
-__device__ __forceinline__ uint4 rms_rope_vec(const uint4& x, __nv_bfloat162 r2, const uint4& g, bool rot, const float2* cs) {
-  const uint32_t xw[4] = {x.x, x.y, x.z, x.w}, gw[4] = {g.x, g.y, g.z, g.w};
-  uint32_t ow[4];
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const __nv_bfloat162 t = __hmul2_rn(__hmul2_rn(as_bf162(xw[q]), r2), as_bf162(gw[q]));
-    if (rot) {
-      const float2 f = __bfloat1622float2(t);
-      ow[q] = vc::pack_bf16x2(f.x * cs[q].x - f.y * cs[q].y, f.x * cs[q].y + f.y * cs[q].x);
-    } else {
-      ow[q] = as_u32(t);
-    }
-  }
-  return make_uint4(ow[0], ow[1], ow[2], ow[3]);
-}
-
-
 // Packed fp32x2 arithmetic (sm_100 FADD2 / FMUL2 / FFMA2: one issue slot for two fp32 lanes).  Per-lane results are those of
 // the scalar instructions (round-to-nearest, ftz as everywhere in this file), so only the ORDER of a reduction can change bits.
 __device__ __forceinline__ float2 add2(float2 a, float2 b) {
@@ -282,6 +271,35 @@ __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
       : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
   return d;
 }
+
+// sum of squares of one 16-byte vector into two packed accumulators (even / odd pairs): 3 issue slots per bf16x2 word.
+// Every RMSNorm kernel of this file (in place: block, ring; Ulysses producers: scatter, bulk scatter) adds in this order, so
+// they stay bit-identical to one another.
+__device__ __forceinline__ void vec_sumsq0(const uint4& u, float2& a0, float2& a1) {
+  const float2 f0 = up2(u.x), f1 = up2(u.y), f2 = up2(u.z), f3 = up2(u.w);
+  a0 = fma2(f0, f0, a0);
+  a1 = fma2(f1, f1, a1);
+  a0 = fma2(f2, f2, a0);
+  a1 = fma2(f3, f3, a1);
+}
+__device__ __forceinline__ float sumsq_total(const float2& a0, const float2& a1) { return (a0.x + a0.y) + (a1.x + a1.y); }
+// one 16-byte vector of q or k: bf(bf(x * r) * g), then the adjacent-pair rotation in fp32 (one rounding at the pack)
+__device__ __forceinline__ uint4 rms_rope_vec(const uint4& x, __nv_bfloat162 r2, const uint4& g, bool rot, const float2* cs) {
+  const uint32_t xw[4] = {x.x, x.y, x.z, x.w}, gw[4] = {g.x, g.y, g.z, g.w};
+  uint32_t ow[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const __nv_bfloat162 t = __hmul2_rn(__hmul2_rn(as_bf162(xw[q]), r2), as_bf162(gw[q]));
+    if (rot) {
+      const float2 f = __bfloat1622float2(t);
+      ow[q] = vc::pack_bf16x2(f.x * cs[q].x - f.y * cs[q].y, f.x * cs[q].y + f.y * cs[q].x);
+    } else {
+      ow[q] = as_u32(t);
+    }
+  }
+  return make_uint4(ow[0], ow[1], ow[2], ow[3]);
+}
+
 
 // LayerNorm of one row held as VPT 16-byte vectors per thread (ROW_NT threads), shared by the register and the ring kernel.
 // Round 2: the row is unpacked to fp32 pairs ONCE and all three passes (sum, centred sum of squares, normalise) run on packed
@@ -361,7 +379,8 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 2) ln_modulate_block_ke
       const int v = threadIdx.x + ROW_NT * i;
       raw[i] = (v < nvec) ? ld_stream(xr + v) : make_uint4(0, 0, 0, 0);
     }
-    const long long batch = (mode == 0) ? row / rows_per_batch : 0;
+    unsigned in_batch_unused;
+    const long long batch = (mode == 0) ? (long long)row_batch(row, rows_per_batch, in_batch_unused) : 0;
     if (batch != cached_batch) {
       cached_batch = batch;
       const uint4* q0 = reinterpret_cast<const uint4*>(p0 + batch * mod_stride);
@@ -414,13 +433,14 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_block_k
     }
   }
   for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
-    const long long pos = pos_offset + (row % rows_per_batch);
-    const bool rot = do_rope && pos < (long long)Fg * Hg * Wg;
+    unsigned in_batch;
+    row_batch(row, rows_per_batch, in_batch);
+    const unsigned pos = (unsigned)pos_offset + in_batch;
+    const bool rot = do_rope && pos < (unsigned)(Fg * Hg * Wg);
     float2 cs[4];
     if (rot) {
-      const int pw = (int)(pos % Wg);
-      const int ph = (int)((pos / Wg) % Hg);
-      const int pf = (int)(pos / ((long long)Wg * Hg));
+      int pf, ph, pw;
+      split_pos(pos, Hg, Wg, pf, ph, pw);
 #pragma unroll
       for (int p = 0; p < 4; ++p) {
         const int j = j0 + p;
@@ -445,9 +465,10 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_block_k
           }
         }
       }
-      float ss = 0.f;
+      float2 sq0 = make_float2(0.f, 0.f), sq1 = make_float2(0.f, 0.f);
 #pragma unroll
-      for (int i = 0; i < VPT; ++i) ss = vec_sumsq0(raw[i], ss);
+      for (int i = 0; i < VPT; ++i) vec_sumsq0(raw[i], sq0, sq1);
+      const float ss = sumsq_total(sq0, sq1);
       const float r = rsqrtf(block_sum(ss, which ? red_b : red_a) * inv_d + eps);
       const __nv_bfloat162 r2 = __floats2bfloat162_rn(r, r);
 #pragma unroll
@@ -507,7 +528,8 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 2) ln_modulate_ring_ker
       vc::bulk_load_1d(ring_smem + (size_t)ns * row_bytes, x + (row + (long long)(RING - 1) * gridDim.x) * ldx, row_bytes,
                        &full[ns]);
     }
-    const long long batch = (mode == 0) ? row / rows_per_batch : 0;
+    unsigned in_batch_unused;
+    const long long batch = (mode == 0) ? (long long)row_batch(row, rows_per_batch, in_batch_unused) : 0;
     if (batch != cached_batch) {
       cached_batch = batch;
       const uint4* q0 = reinterpret_cast<const uint4*>(p0 + batch * mod_stride);
@@ -586,12 +608,13 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_ring_ke
       vc::bulk_load_1d(ring_smem + (size_t)ns * row_bytes, seg_ptr(g + RING - 1), row_bytes, &full[ns]);
     }
     if (which == 0) {
-      const long long pos = pos_offset + (row % rows_per_batch);
-      rot = do_rope && pos < (long long)Fg * Hg * Wg;
+      unsigned in_batch;
+      row_batch(row, rows_per_batch, in_batch);
+      const unsigned pos = (unsigned)pos_offset + in_batch;
+      rot = do_rope && pos < (unsigned)(Fg * Hg * Wg);
       if (rot) {
-        const int pw = (int)(pos % Wg);
-        const int ph = (int)((pos / Wg) % Hg);
-        const int pf = (int)(pos / ((long long)Wg * Hg));
+        int pf, ph, pw;
+        split_pos(pos, Hg, Wg, pf, ph, pw);
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
           const int j = j0 + p;
@@ -608,9 +631,10 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_ring_ke
       const int v = threadIdx.x + ROW_NT * i;
       raw[i] = (v < nvec) ? xs[v] : make_uint4(0, 0, 0, 0);
     }
-    float ss = 0.f;
+    float2 sq0 = make_float2(0.f, 0.f), sq1 = make_float2(0.f, 0.f);
 #pragma unroll
-    for (int i = 0; i < VPT; ++i) ss = vec_sumsq0(raw[i], ss);
+    for (int i = 0; i < VPT; ++i) vec_sumsq0(raw[i], sq0, sq1);
+    const float ss = sumsq_total(sq0, sq1);
     const float r = rsqrtf(block_sum(ss, (g & 1) ? red_b : red_a) * inv_d + eps);
     const __nv_bfloat162 r2 = __floats2bfloat162_rn(r, r);
     uint4* xr = reinterpret_cast<uint4*>(qkv + row * ld + (long long)which * D);
@@ -653,14 +677,14 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_scatter
   const float2* tab_w = tab_h + (long long)Hg * nh;
   const int j0 = ((threadIdx.x * 8) % (2 * half_d)) >> 1;
   for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
-    const long long b = row / rows_per_batch;
-    const long long pos = pos_offset + (row - b * rows_per_batch);
+    unsigned in_batch;
+    const long long b = row_batch(row, rows_per_batch, in_batch);
+    const long long pos = (long long)((unsigned)pos_offset + in_batch);
     const bool rot = pos < (long long)Fg * Hg * Wg;
     float2 cs[4];
     if (rot) {
-      const int pw = (int)(pos % Wg);
-      const int ph = (int)((pos / Wg) % Hg);
-      const int pf = (int)(pos / ((long long)Wg * Hg));
+      int pf, ph, pw;
+      split_pos((unsigned)pos, Hg, Wg, pf, ph, pw);
 #pragma unroll
       for (int p = 0; p < 4; ++p) {
         const int j = j0 + p;
@@ -684,9 +708,10 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 8 : 7) rmsnorm_rope_scatter
       }
       __nv_bfloat162 r2 = __floats2bfloat162_rn(1.0f, 1.0f);
       if (which < 2) {
-        float ss = 0.f;
+        float2 sq0 = make_float2(0.f, 0.f), sq1 = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int i = 0; i < VPT; ++i) ss = vec_sumsq0(raw[i], ss);
+        for (int i = 0; i < VPT; ++i) vec_sumsq0(raw[i], sq0, sq1);
+        const float ss = sumsq_total(sq0, sq1);
         const float r = rsqrtf(block_sum(ss, red[n_red & 1]) * inv_d + eps);
         ++n_red;
         r2 = __floats2bfloat162_rn(r, r);
@@ -734,14 +759,14 @@ __global__ void __launch_bounds__(ROW_NT, 8) rmsnorm_rope_scatter_bulk_kernel(
   const int j0 = ((threadIdx.x * 8) % (2 * half_d)) >> 1;
   int seg = 0;  // segments (row, matrix) handled by this CTA so far: staging slot = seg & 1
   for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
-    const long long b = row / rows_per_batch;
-    const long long pos = pos_offset + (row - b * rows_per_batch);
+    unsigned in_batch;
+    const long long b = row_batch(row, rows_per_batch, in_batch);
+    const long long pos = (long long)((unsigned)pos_offset + in_batch);
     const bool rot = pos < (long long)Fg * Hg * Wg;
     float2 cs[4];
     if (rot) {
-      const int pw = (int)(pos % Wg);
-      const int ph = (int)((pos / Wg) % Hg);
-      const int pf = (int)(pos / ((long long)Wg * Hg));
+      int pf, ph, pw;
+      split_pos((unsigned)pos, Hg, Wg, pf, ph, pw);
 #pragma unroll
       for (int p = 0; p < 4; ++p) {
         const int j = j0 + p;
@@ -761,11 +786,12 @@ __global__ void __launch_bounds__(ROW_NT, 8) rmsnorm_rope_scatter_bulk_kernel(
         const int v = threadIdx.x + ROW_NT * i;
         raw[i] = (v < nvec) ? ld_stream(xr + v) : make_uint4(0, 0, 0, 0);
       }
-      float ss = 0.f;
+      float2 sq0 = make_float2(0.f, 0.f), sq1 = make_float2(0.f, 0.f);
       if (which < 2) {
 #pragma unroll
-        for (int i = 0; i < VPT; ++i) ss = vec_sumsq0(raw[i], ss);
+        for (int i = 0; i < VPT; ++i) vec_sumsq0(raw[i], sq0, sq1);
       }
+      const float ss = sumsq_total(sq0, sq1);
       // staging slot seg & 1 was last used by segment seg - 2: its bulk stores must have read it out.  Thread 0 waits, the
       // block-wide sync inside block_sum publishes that (for v the sum itself is unused).
       if (threadIdx.x == 0) vc::bulk_wait_group_read<1>();
@@ -888,6 +914,7 @@ int vc_ln_modulate(const void* x, long long ldx, void* out, long long ldo, const
   VC_CHECK_ARG(x && out && shift_or_beta && scale_or_gamma, "vc_ln_modulate: null pointer");
   VC_CHECK_ARG(D > 0 && D % 8 == 0 && D <= 8192, "vc_ln_modulate: D=%d must be a multiple of 8 and <= 8192", D);
   VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && ldx % 8 == 0 && ldo % 8 == 0, "vc_ln_modulate: bad rows/strides");
+  VC_CHECK_ARG(rows < (1LL << 31) && rows_per_batch < (1LL << 31), "vc_ln_modulate: rows must be < 2^31");
   const bool force_regs = (mode & 16) != 0;  // schedule bits (A/B, tests): 16 = register-resident kernel, 32 = row ring
   const bool force_ring = (mode & 32) != 0;
   mode &= ~48;
@@ -950,6 +977,9 @@ int vc_rmsnorm_rope_qk(void* qkv, long long ld, long long rows, long long rows_p
                                D % (2 * (nf + nh + nw)) == 0),
                "vc_rmsnorm_rope_qk: bad rope table split");
   VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && pos_offset >= 0, "vc_rmsnorm_rope_qk: bad rows");
+  VC_CHECK_ARG(rows < (1LL << 31) && pos_offset + rows_per_batch < (1LL << 31) &&
+                   (!apply_rope || (long long)grid_f * grid_h * grid_w < (1LL << 31)),
+               "vc_rmsnorm_rope_qk: rows, positions and the grid volume must be < 2^31");
   if (rows == 0) return 0;
   // The in-place RMSNorm(+RoPE) keeps the register-resident kernel (it already prefetches the next segment into registers):
   // the ring variant is on par alone at D = 5120 (5.80 vs 5.76 TB/s) but slower in the step (4.29 vs 4.77 TB/s) and at
@@ -1021,6 +1051,8 @@ int vc_rmsnorm_rope_qkv_scatter(const void* qkv, long long ld, long long rows, l
   VC_CHECK_ARG(rows >= 0 && rows_per_batch > 0 && rows % rows_per_batch == 0 && pos_offset >= 0 &&
                    pos_offset + rows_per_batch <= l_total,
                "vc_rmsnorm_rope_qkv_scatter: bad rows / positions");
+  VC_CHECK_ARG(rows < (1LL << 31) && l_total < (1LL << 31) && (long long)grid_f * grid_h * grid_w < (1LL << 31),
+               "vc_rmsnorm_rope_qkv_scatter: rows, positions and the grid volume must be < 2^31");
   if (rows == 0) return 0;
   PeerPtrs pp;
   for (int i = 0; i < 8; ++i) pp.p[i] = (__nv_bfloat16*)(i < n_peers ? peer_recv[i] : nullptr);
