@@ -413,81 +413,74 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_block_k
     __nv_bfloat16* __restrict__ qkv, long long ld, long long rows, long long rows_per_batch, long long pos_offset, int D,
     const __nv_bfloat16* __restrict__ gq, const __nv_bfloat16* __restrict__ gk, const float2* __restrict__ tab, int Fg,
     int Hg, int Wg, int nf, int nh, int nw, float eps, int do_rope, int n_mats) {
-  __shared__ float red[2][ROW_NT / 32];   // alternate per segment: a buffer is rewritten two block syncs after its reads
+  __shared__ float red_a[ROW_NT / 32], red_b[ROW_NT / 32];
   const int nvec = D >> 3;
   const float inv_d = 1.0f / (float)D;
   const int half_d = nf + nh + nw;
-  // A thread's four (cos, sin) pairs sit at fixed columns j0..j0+3 of the head for every row, so which axis table a pair
-  // comes from, its column inside that table and the table's row stride are loop invariants: per row only the table ROW
-  // (frame, height or width index) changes.
-  const float2* tcol[4];
-  int taxis[4], tstride[4];
-  {
-    const int j0 = do_rope ? (((threadIdx.x * 8) % (2 * half_d)) >> 1) : 0;
-#pragma unroll
-    for (int p = 0; p < 4; ++p) {
-      const int j = j0 + p;
-      if (j < nf) { taxis[p] = 0; tstride[p] = nf; tcol[p] = tab + j; }
-      else if (j < nf + nh) { taxis[p] = 1; tstride[p] = nh; tcol[p] = tab + (long long)Fg * nf + (j - nf); }
-      else { taxis[p] = 2; tstride[p] = nw; tcol[p] = tab + (long long)Fg * nf + (long long)Hg * nh + (j - nf - nh); }
-    }
-  }
-  const long long my_rows = rows > (long long)blockIdx.x ? (rows - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-  const long long my_segs = my_rows * n_mats;
-  // segment g of this CTA: (row, q | k)
-  auto seg_row = [&](long long g) { return (long long)blockIdx.x + (n_mats == 2 ? (g >> 1) : g) * gridDim.x; };
-  auto seg_which = [&](long long g) { return n_mats == 2 ? (int)(g & 1) : 0; };
-  auto load = [&](uint4 (&buf)[VPT], long long g) {
-    const uint4* xs = reinterpret_cast<const uint4*>(qkv + seg_row(g) * ld + (long long)seg_which(g) * D);
+  const float2* tab_f = tab;
+  const float2* tab_h = tab + (long long)Fg * nf;
+  const float2* tab_w = tab_h + (long long)Hg * nh;
+  const int j0 = do_rope ? (((threadIdx.x * 8) % (2 * half_d)) >> 1) : 0;
+  // software pipeline over (row, q|k) segments: the next segment's loads are issued before the current one's
+  // reduction, so a CTA always has two segments of HBM reads in flight
+  uint4 raw[VPT], nxt[VPT];
+  if ((long long)blockIdx.x < rows) {
+    const uint4* x0 = reinterpret_cast<const uint4*>(qkv + (long long)blockIdx.x * ld);
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
       const int v = threadIdx.x + ROW_NT * i;
-      buf[i] = (v < nvec) ? ld_stream_rw(xs + v) : make_uint4(0, 0, 0, 0);
+      raw[i] = (v < nvec) ? ld_stream_rw(x0 + v) : make_uint4(0, 0, 0, 0);
     }
-  };
-  float2 cs[4];
-  bool rot = false;
-  auto process = [&](const uint4 (&buf)[VPT], long long g) {
-    const long long row = seg_row(g);
-    const int which = seg_which(g);
-    if (which == 0) {   // per-row state, shared by the q and the k segment
-      unsigned in_batch;
-      row_batch(row, rows_per_batch, in_batch);
-      const unsigned pos = (unsigned)pos_offset + in_batch;
-      rot = do_rope && pos < (unsigned)(Fg * Hg * Wg);
-      if (rot) {
-        int pf, ph, pw;
-        split_pos(pos, Hg, Wg, pf, ph, pw);
+  }
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    unsigned in_batch;
+    row_batch(row, rows_per_batch, in_batch);
+    const unsigned pos = (unsigned)pos_offset + in_batch;
+    const bool rot = do_rope && pos < (unsigned)(Fg * Hg * Wg);
+    float2 cs[4];
+    if (rot) {
+      int pf, ph, pw;
+      split_pos(pos, Hg, Wg, pf, ph, pw);
 #pragma unroll
-        for (int p = 0; p < 4; ++p) cs[p] = __ldg(tcol[p] + (taxis[p] == 0 ? pf : taxis[p] == 1 ? ph : pw) * tstride[p]);
+      for (int p = 0; p < 4; ++p) {
+        const int j = j0 + p;
+        if (j < nf) cs[p] = __ldg(tab_f + pf * nf + j);
+        else if (j < nf + nh) cs[p] = __ldg(tab_h + ph * nh + (j - nf));
+        else cs[p] = __ldg(tab_w + pw * nw + (j - nf - nh));
       }
     }
-    uint4* xr = reinterpret_cast<uint4*>(qkv + row * ld + (long long)which * D);
-    const uint4* gr = reinterpret_cast<const uint4*>(which == 0 ? gq : gk);
-    float2 sq0 = make_float2(0.f, 0.f), sq1 = make_float2(0.f, 0.f);
+#pragma unroll 1
+    for (int which = 0; which < n_mats; ++which) {
+      uint4* xr = reinterpret_cast<uint4*>(qkv + row * ld + (long long)which * D);
+      const uint4* gr = reinterpret_cast<const uint4*>(which == 0 ? gq : gk);
+      {  // prefetch the next segment: k of this row, else q of this CTA's next row
+        const bool same_row = which + 1 < n_mats;
+        const long long nrow = same_row ? row : row + gridDim.x;
+        if (nrow < rows) {
+          const uint4* xn = reinterpret_cast<const uint4*>(qkv + nrow * ld + (same_row ? (long long)(which + 1) * D : 0));
 #pragma unroll
-    for (int i = 0; i < VPT; ++i) vec_sumsq0(buf[i], sq0, sq1);
-    const float r = rsqrtf(block_sum(sumsq_total(sq0, sq1), red[g & 1]) * inv_d + eps);
-    const __nv_bfloat162 r2 = __floats2bfloat162_rn(r, r);
+          for (int i = 0; i < VPT; ++i) {
+            const int v = threadIdx.x + ROW_NT * i;
+            nxt[i] = (v < nvec) ? ld_stream_rw(xn + v) : make_uint4(0, 0, 0, 0);
+          }
+        }
+      }
+      float2 sq0 = make_float2(0.f, 0.f), sq1 = make_float2(0.f, 0.f);
 #pragma unroll
-    for (int i = 0; i < VPT; ++i) {
-      const int v = threadIdx.x + ROW_NT * i;
-      if (v < nvec) st_stream(xr + v, rms_rope_vec(buf[i], r2, __ldg(gr + v), rot, cs));
+      for (int i = 0; i < VPT; ++i) vec_sumsq0(raw[i], sq0, sq1);
+      const float ss = sumsq_total(sq0, sq1);
+      const float r = rsqrtf(block_sum(ss, which ? red_b : red_a) * inv_d + eps);
+      const __nv_bfloat162 r2 = __floats2bfloat162_rn(r, r);
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + ROW_NT * i;
+        if (v < nvec) st_stream(xr + v, rms_rope_vec(raw[i], r2, __ldg(gr + v), rot, cs));
+      }
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) raw[i] = nxt[i];
+      if (n_mats == 1) __syncthreads();  // red_a is reused by the next row
     }
-  };
-  // Two register buffers in ping-pong over the segment sequence (round 2: the single-buffer pipeline copied the prefetched
-  // segment into place, 20 MOVs per segment): while segment g is reduced and written from one buffer, segment g+1 streams
-  // into the other, so a CTA always has two segments of HBM reads in flight.
-  uint4 bufA[VPT], bufB[VPT];
-  if (my_segs > 0) load(bufA, 0);
-  long long g = 0;
-  for (; g + 1 < my_segs; g += 2) {
-    load(bufB, g + 1);
-    process(bufA, g);
-    if (g + 2 < my_segs) load(bufA, g + 2);
-    process(bufB, g + 1);
   }
-  if (g < my_segs) process(bufA, g);
 }
 
 // ----------------------------------------------------------------------------------------------------
