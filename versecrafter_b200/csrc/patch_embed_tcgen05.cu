@@ -191,34 +191,48 @@ patch_embed_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     __nv_bfloat16* crow = p.out + (row_ok ? token - p.tok_lo : 0) * p.ldo;
     int acc = 0;
     uint32_t acc_phase = 0;
+    auto load_bias = [&](int n) {   // lane l holds bias[n*BN + 8l .. +8)
+      const int col = n * BN + lane * 8;
+      return col < p.N ? __ldg(reinterpret_cast<const uint4*>(p.bias + col)) : make_uint4(0u, 0u, 0u, 0u);
+    };
+    uint4 bias_cur = load_bias(n_begin);
     for (int n = n_begin; n < n_end; ++n) {
+      const uint4 bias_nxt = n + 1 < n_end ? load_bias(n + 1) : make_uint4(0u, 0u, 0u, 0u);
       vc::mbar_wait(&acc_full[acc], acc_phase);
       vc::tc_fence_after();
       const uint32_t t_addr = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t rg[32];
-        vc::tmem_ld32(t_addr + c * 32, rg);
-        vc::tmem_ld_wait();
-        const int col0 = n * BN + c * 32;
-        if (row_ok && col0 < p.N) {
+      // Round 2.  The ncu source page of the first form (tcgen05.ld, wait, bias load, use) put half of all stall samples on
+      // the first use of the bias registers: the epilogue, not the tensor pipe (24 % active), set the pace.  Now
+      //   * the tile's 256 bias values are fetched ONCE per tile, one 16-byte vector per lane, a whole tile ahead
+      //     (bias_nxt below), and handed to the lanes that need them by warp shuffles: no global load in the chunk loop;
+      //   * the TMEM load of chunk c+1 is issued before chunk c is converted and stored.
+      uint32_t rg[2][32];
+      vc::tmem_ld32(t_addr, rg[0]);
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const int col = col0 + g * 8;
-            if (col < p.N) {
-              const uint4 bu = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
-              const float2 b0 = vc::unpack_bf16x2(bu.x), b1 = vc::unpack_bf16x2(bu.y), b2 = vc::unpack_bf16x2(bu.z),
-                           b3 = vc::unpack_bf16x2(bu.w);
-              uint4 o;
-              o.x = vc::pack_bf16x2(__uint_as_float(rg[g * 8 + 0]) + b0.x, __uint_as_float(rg[g * 8 + 1]) + b0.y);
-              o.y = vc::pack_bf16x2(__uint_as_float(rg[g * 8 + 2]) + b1.x, __uint_as_float(rg[g * 8 + 3]) + b1.y);
-              o.z = vc::pack_bf16x2(__uint_as_float(rg[g * 8 + 4]) + b2.x, __uint_as_float(rg[g * 8 + 5]) + b2.y);
-              o.w = vc::pack_bf16x2(__uint_as_float(rg[g * 8 + 6]) + b3.x, __uint_as_float(rg[g * 8 + 7]) + b3.y);
-              *reinterpret_cast<uint4*>(crow + col) = o;
-            }
+      for (int c = 0; c < BN / 32; ++c) {
+        vc::tmem_ld_wait();
+        if (c + 1 < BN / 32) vc::tmem_ld32(t_addr + (c + 1) * 32, rg[(c + 1) & 1]);
+        const uint32_t(&r)[32] = rg[c & 1];
+        const int col0 = n * BN + c * 32;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int src = c * 4 + g;   // lane holding columns [n*BN + src*8, +8)
+          const uint32_t bx = __shfl_sync(0xffffffffu, bias_cur.x, src), by = __shfl_sync(0xffffffffu, bias_cur.y, src);
+          const uint32_t bz = __shfl_sync(0xffffffffu, bias_cur.z, src), bw = __shfl_sync(0xffffffffu, bias_cur.w, src);
+          const int col = col0 + g * 8;
+          if (row_ok && col < p.N) {
+            const float2 b0 = vc::unpack_bf16x2(bx), b1 = vc::unpack_bf16x2(by), b2 = vc::unpack_bf16x2(bz),
+                         b3 = vc::unpack_bf16x2(bw);
+            uint4 o;
+            o.x = vc::pack_bf16x2(__uint_as_float(r[g * 8 + 0]) + b0.x, __uint_as_float(r[g * 8 + 1]) + b0.y);
+            o.y = vc::pack_bf16x2(__uint_as_float(r[g * 8 + 2]) + b1.x, __uint_as_float(r[g * 8 + 3]) + b1.y);
+            o.z = vc::pack_bf16x2(__uint_as_float(r[g * 8 + 4]) + b2.x, __uint_as_float(r[g * 8 + 5]) + b2.y);
+            o.w = vc::pack_bf16x2(__uint_as_float(r[g * 8 + 6]) + b3.x, __uint_as_float(r[g * 8 + 7]) + b3.y);
+            *reinterpret_cast<uint4*>(crow + col) = o;
           }
         }
       }
+      bias_cur = bias_nxt;
       vc::tc_fence_before();
       vc::mbar_arrive(&acc_empty[acc]);
       acc ^= 1;
