@@ -417,10 +417,21 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_block_k
   const int nvec = D >> 3;
   const float inv_d = 1.0f / (float)D;
   const int half_d = nf + nh + nw;
-  const float2* tab_f = tab;
-  const float2* tab_h = tab + (long long)Fg * nf;
-  const float2* tab_w = tab_h + (long long)Hg * nh;
-  const int j0 = do_rope ? (((threadIdx.x * 8) % (2 * half_d)) >> 1) : 0;
+  // A thread's four (cos, sin) pairs sit at fixed columns j0..j0+3 of the head for every row, so which axis table a pair comes
+  // from, its column inside that table and the table's row stride are loop invariants: per row only the table ROW (frame,
+  // height or width index) changes.
+  const float2* tcol[4];
+  int taxis[4], tstride[4];
+  {
+    const int j0 = do_rope ? (((threadIdx.x * 8) % (2 * half_d)) >> 1) : 0;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int j = j0 + p;
+      if (j < nf) { taxis[p] = 0; tstride[p] = nf; tcol[p] = tab + j; }
+      else if (j < nf + nh) { taxis[p] = 1; tstride[p] = nh; tcol[p] = tab + (long long)Fg * nf + (j - nf); }
+      else { taxis[p] = 2; tstride[p] = nw; tcol[p] = tab + (long long)Fg * nf + (long long)Hg * nh + (j - nf - nh); }
+    }
+  }
   // software pipeline over (row, q|k) segments: the next segment's loads are issued before the current one's
   // reduction, so a CTA always has two segments of HBM reads in flight
   uint4 raw[VPT], nxt[VPT];
@@ -442,12 +453,7 @@ __global__ void __launch_bounds__(ROW_NT, VPT <= 5 ? 5 : 4) rmsnorm_rope_block_k
       int pf, ph, pw;
       split_pos(pos, Hg, Wg, pf, ph, pw);
 #pragma unroll
-      for (int p = 0; p < 4; ++p) {
-        const int j = j0 + p;
-        if (j < nf) cs[p] = __ldg(tab_f + pf * nf + j);
-        else if (j < nf + nh) cs[p] = __ldg(tab_h + ph * nh + (j - nf));
-        else cs[p] = __ldg(tab_w + pw * nw + (j - nf - nh));
-      }
+      for (int p = 0; p < 4; ++p) cs[p] = __ldg(tcol[p] + (taxis[p] == 0 ? pf : taxis[p] == 1 ? ph : pw) * tstride[p]);
     }
 #pragma unroll 1
     for (int which = 0; which < n_mats; ++which) {
