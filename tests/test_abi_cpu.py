@@ -29,6 +29,48 @@ def test_library_exports_every_declared_symbol(lib):
     assert set(SIGNATURES) == declared
 
 
+def test_ctypes_table_matches_the_header_prototypes():
+    """Every prototype of include/vc_b200.h against versecrafter_b200/_lib.SIGNATURES: same number of arguments, and each
+    argument of the same kind (pointer / 64-bit integer / 32-bit integer / float) — a drift here would not fail to load, it
+    would pass garbage to a kernel launcher."""
+    from versecrafter_b200._lib import SIGNATURES
+    hdr = open(os.path.join(ROOT, "include", "vc_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    hdr = "\n".join(l for l in hdr.splitlines() if not l.lstrip().startswith("#"))
+    protos = re.findall(r"([A-Za-z_][A-Za-z0-9_ \*]*?)\b(vc_[a-z0-9_]+)\s*\(([^)]*)\)\s*;", hdr, flags=re.S)
+    assert len(protos) == len(SIGNATURES)
+
+    def kind_c(decl):
+        decl = " ".join(decl.split())
+        if decl == "void" or not decl:
+            return None
+        if "*" in decl:
+            return "ptr"
+        base = decl.rsplit(" ", 1)[0] if " " in decl else decl
+        if "long long" in base:
+            return "i64"
+        if "float" in base:
+            return "f32"
+        if "double" in base:
+            return "f64"
+        if "int" in base or "unsigned" in base:
+            return "i32"
+        raise AssertionError(f"unclassified parameter {decl!r}")
+
+    def kind_ct(t):
+        if t in (ctypes.c_void_p, ctypes.c_char_p) or hasattr(t, "_type_") and not isinstance(t._type_, str):
+            return "ptr"
+        return {ctypes.c_longlong: "i64", ctypes.c_int: "i32", ctypes.c_uint: "i32", ctypes.c_float: "f32",
+                ctypes.c_double: "f64"}[t]
+
+    for ret, name, args in protos:
+        want = [k for k in (kind_c(a) for a in args.split(",")) if k]
+        res, argtypes = SIGNATURES[name]
+        got = [kind_ct(t) for t in argtypes]
+        assert got == want, f"{name}: header {want} vs ctypes {got}"
+        assert (kind_ct(res) == "ptr") == ("*" in ret), name
+
+
 def test_version_and_arch(lib):
     assert lib.vc_version() >= 100
     assert lib.vc_build_arch() == 100  # sm_100a only
