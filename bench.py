@@ -300,7 +300,13 @@ def run_gpu_arm(args):
         ctx = [c.cuda(non_blocking=True) for c in host["ctx"]]
         t = host["t"].cuda(non_blocking=True)
         y = model(x=x, t=t, geoada_context=geo, context=ctx, seq_len=host["seq_len"], geoada_context_scale=1.0)
-        return y.cpu()
+        # device -> host read of the step's result into a pinned buffer allocated once (a fresh pageable tensor per step
+        # would add its allocation and first-touch page faults to every step)
+        if host.get("y") is None or host["y"].shape != y.shape:
+            host["y"] = torch.empty(y.shape, dtype=y.dtype, pin_memory=True)
+        host["y"].copy_(y, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return host["y"]
 
     def barrier():
         if world > 1:
