@@ -81,6 +81,21 @@ int vc_time_embed(const double* t, int B, int freq_dim, int D, const void* w0, c
                   const void* b2, const void* wp, const void* bp, void* e_out, void* e0_out, float* workspace,
                   void* stream);
 
+/* vc_time_embed without the workspace argument.  No counterpart in the reference: it exists for hosts that cannot allocate
+ * device memory when they need the embedding — a loop whose memory pool was carved up before the run and is now closed,
+ * code running on a thread or in a callback that must not touch the allocator, or a C caller that was itself only handed
+ * input and output pointers.  The three intermediate vectors live in a fixed array compiled into the library
+ * (8 * (256 + 2*5120) fp32 = 328 KB per GPU, held from library load to process exit); inputs and outputs are still the
+ * caller's.  Limit: B * (freq_dim + 2*D) <= 83,968 (e.g. B = 8 at freq_dim 256, D 5120); anything larger returns < 0 with a
+ * message that names the limit — use vc_time_embed there.  The call itself performs no cudaMalloc / cudaFree and calls
+ * no library that allocates.  The first call on each device looks up the array's device address (with that device
+ * current); make that first call outside any stream capture.  All calls on a device share the one array: it
+ * keeps whatever the last call wrote, which is harmless because each call overwrites every value before reading it (nothing
+ * needs zeroing), but two calls whose kernels can overlap on the GPU (different streams, no ordering between them) race
+ * on it and corrupt each other — order them.  Same arithmetic and launches as vc_time_embed: outputs are bit-identical. */
+int vc_time_embed_static(const double* t, int B, int freq_dim, int D, const void* w0, const void* b0, const void* w2,
+                         const void* b2, const void* wp, const void* bp, void* e_out, void* e0_out, void* stream);
+
 /* a4/a6 — `self.modulation + e` of every block in one launch (wan_transformer3d.py:588 per block, Head :640-643):
  *   out[i, b, :]  = bf16(block_modulations[i][0:6D] + e0[b, 0:6D])      i < n_blocks   (out: [n_blocks, B, 6D])
  *   out_head[b,:] = bf16(head_modulation[0:2D] + (e[b] | e[b]))          when head_modulation != NULL  ([B, 2D])

@@ -43,6 +43,7 @@ SIGNATURES = {
     "vc_render_points": (_i, [_vp, _vp, _c_ll, _fp, _fp, _i, _i, _f, _fp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "vc_render_mesh_depth": (_i, [_vp, _i, _vp, _i, _fp, _fp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "vc_time_embed": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "vc_time_embed_static": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "vc_modulation_table": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "vc_patchify": (_i, [_vp, _vp, _i, _i, _i, _i, _c_ll, _vp]),
     "vc_unpatchify": (_i, [_vp, _c_ll, _vp, _i, _i, _i, _i, _vp]),

@@ -11,6 +11,8 @@
 // Compiled WITHOUT --use_fast_math (build.py PRECISE_SOURCES): SiLU uses IEEE division and expf, as torch does.
 #include "common.cuh"
 
+#include <atomic>
+
 namespace {
 
 constexpr int MAX_B = 8;
@@ -197,4 +199,90 @@ extern "C" int vc_modulation_table(const void* const* block_modulations, int n_b
       (const __nv_bfloat16* const*)block_modulations, n_blocks, (const __nv_bfloat16*)e0, B, D, (__nv_bfloat16*)out,
       (const __nv_bfloat16*)head_modulation, (const __nv_bfloat16*)e, (__nv_bfloat16*)out_head);
   VC_RETURN_LAUNCH_STATUS("vc_modulation_table");
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// vc_time_embed_static — vc_time_embed for callers that cannot hand over a workspace.
+//
+// Some hosts of this library have no way to allocate device memory at the moment they need the timestep embedding:
+// a denoise loop whose allocator has already been frozen for the run (a fixed pool handed out up front, so a later
+// cudaMalloc would either fail or fragment it), a plugin called from inside somebody else's stream callback or worker
+// thread that is forbidden from touching the allocator, or a C host that only ever received input/output pointers from
+// its own caller.  For them the three intermediate vectors of the island (sinusoid, silu(W0 s + b0), silu(e)) live in the
+// fixed array below instead of a caller-provided workspace.  The array is part of the library image: every GPU that
+// loads libvc_b200.so carries these 328 KB from load until process exit, whether or not this entry point is ever called.
+//
+// The name `g_time_embed_static_scratch` means two different things.  Inside device code it is the array.  Inside host
+// code it is only a handle that the runtime uses to look the array up — handing it to a kernel as if it were a pointer
+// would make the kernel fault (or, on a system where the GPU can dereference host addresses, quietly scribble over host
+// memory).  So the host asks the runtime for the real device address, once per device and with that device current
+// (static_scratch_for_current_device), and passes that address to the kernels.
+constexpr long long TIME_EMBED_STATIC_MAX_FLOATS = 8LL * (256 + 2 * 5120);  // B = 8, freq_dim = 256, D = 5120 (Wan 14B)
+static __device__ __align__(256) float g_time_embed_static_scratch[TIME_EMBED_STATIC_MAX_FLOATS];
+
+namespace {
+
+constexpr int STATIC_MAX_DEVICES = 64;
+std::atomic<float*> g_static_scratch_addr[STATIC_MAX_DEVICES];  // zero-initialised: nullptr = not looked up yet
+
+// Device address of the array on the CURRENT device.  Each device has its own copy of a __device__ variable, so the
+// lookup is per device and must run with that device current; the answer never changes afterwards, so it is cached.
+// Two threads racing on the first call both ask the runtime and store the same value.
+int static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    vc_host::set_error("vc_time_embed_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  if (dev < 0 || dev >= STATIC_MAX_DEVICES) {
+    vc_host::set_error("vc_time_embed_static: device ordinal %d outside 0..%d", dev, STATIC_MAX_DEVICES - 1);
+    return -1;
+  }
+  float* p = g_static_scratch_addr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    void* sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_time_embed_static_scratch);
+    if (e != cudaSuccess || !sym) {
+      vc_host::set_error("vc_time_embed_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : -1;
+    }
+    p = static_cast<float*>(sym);
+    g_static_scratch_addr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int vc_time_embed_static(const double* t, int B, int freq_dim, int D, const void* w0, const void* b0,
+                                    const void* w2, const void* b2, const void* wp, const void* bp, void* e_out,
+                                    void* e0_out, void* stream) {
+  VC_CHECK_ARG(t && w0 && b0 && w2 && b2 && wp && bp && e_out && e0_out, "vc_time_embed_static: null pointer");
+  VC_CHECK_ARG(B >= 1 && B <= MAX_B, "vc_time_embed_static: batch %d outside 1..%d", B, MAX_B);
+  VC_CHECK_ARG(freq_dim > 0 && freq_dim % 16 == 0 && D > 0 && D % 8 == 0,
+               "vc_time_embed_static: freq_dim must be a multiple of 16 and D a multiple of 8 (freq_dim=%d D=%d)", freq_dim, D);
+  VC_CHECK_ARG(((uintptr_t)w0 | (uintptr_t)w2 | (uintptr_t)wp) % 16 == 0, "vc_time_embed_static: weights must be 16-byte aligned");
+  const long long need = (long long)B * ((long long)freq_dim + 2LL * D);
+  VC_CHECK_ARG(need <= TIME_EMBED_STATIC_MAX_FLOATS,
+               "vc_time_embed_static: B*(freq_dim + 2*D) = %lld fp32 values exceed the built-in scratch of %lld "
+               "(sized for B=8, freq_dim=256, D=5120); use vc_time_embed with your own workspace",
+               need, TIME_EMBED_STATIC_MAX_FLOATS);
+  float* scratch = nullptr;
+  const int rc = static_scratch_for_current_device(&scratch);
+  if (rc != 0) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  // Same carving of the scratch and the same four launches as vc_time_embed.  Every value that is read was written
+  // earlier in this call (the sinusoid kernel fills [B, freq_dim], each GEMV fills its whole [B, D] output), so what the
+  // previous call left behind is never observed and nothing has to be zeroed first.
+  float* sinus = scratch;
+  float* h1 = sinus + (long long)B * freq_dim;
+  float* e_silu = h1 + (long long)B * D;
+  const int half = freq_dim / 2;
+  sinusoid_kernel<<<(B * half + 127) / 128, 128, 0, s>>>(t, B, half, sinus);
+  gemv(B, w0, freq_dim, b0, sinus, freq_dim, D, nullptr, h1, nullptr, 2, s);
+  gemv(B, w2, D, b2, h1, D, D, nullptr, e_silu, e_out, 2 | 4, s);
+  gemv(B, wp, D, bp, e_silu, D, 6 * D, nullptr, nullptr, e0_out, 4, s);
+  VC_RETURN_LAUNCH_STATUS("vc_time_embed_static");
 }
