@@ -135,17 +135,19 @@ def bench_config(name, world):
             "teacache": "off", "cfg_skip": "off", "step_cache": "off", "weights": "random non-trivial bf16 (synthetic_init_)"}
 
 
-def cpu_reference_sample(cfg_name, steps=1, warmup=0, total_budget=150.0, max_step_seconds=28.0):
-    """CPU arm.  One "step" = one DiT block at the config's real width on a bounded sample of its token grid, fp32, on
-    all host cores — the reference's OWN `WanAttentionBlock.forward` (wan_transformer3d.py:564-611), imported unmodified
-    from /root/reference or its byte-for-byte copy under oracle/_ref (kind "reference"; attention() = torch SDPA, VideoX-Fun
-    being un-vendored), else the oracle's restatement (kind "port").  The sample = the first `frames` latent frames of the
-    real H'xW' grid, `frames` chosen from a 1-frame calibration so that one step takes about
-    min(max_step_seconds, total_budget / (steps + warmup)) seconds: exactly `warmup` + `steps` steps run within the budget.
+def cpu_reference_sample(cfg_name, steps=2, total_budget=90.0, max_step_seconds=28.0):
+    """CPU arm.  One "step" = one DiT block at the config's real width, fp32, on all host cores — the reference's OWN
+    `WanAttentionBlock.forward` (wan_transformer3d.py:564-611), imported unmodified from /root/reference or its byte-for-byte
+    copy under oracle/_ref (kind "reference"; attention() = torch SDPA, VideoX-Fun being un-vendored), else the oracle's
+    restatement (kind "port").  The sample does NOT depend on --steps / --warmup: it is the config's FULL token grid whenever
+    a 1-frame calibration says one full block fits max_step_seconds (c3 on 16 cores: 13-19 s), else the first `frames`
+    latent frames of the real H'xW' grid that do.  Only the NUMBER of timed blocks follows `steps`, capped by total_budget
+    (at least one; the calibration runs are the warm-up), so every caller on one box measures the same thing.
     Extrapolation to the metric (stated in `sample`): seconds per FULL-grid block = measured s/step x flops(full grid) /
-    flops(sample) (attention is quadratic in the token count); a denoise step = that x (num_layers + geoada blocks) x CFG
-    batch 2; tokens/s = 2 L / s_per_denoise_step.  Embeddings, adapter projections and the hint copies are left out
-    (generous to the CPU).  Returns (cpu_baseline dict, mean measured seconds per step, extrapolated s per denoise step)."""
+    flops(sample) (x1 when the full grid ran; attention is quadratic in the token count); a denoise step = that x
+    (num_layers + geoada blocks) x CFG batch 2; tokens/s = 2 L / s_per_denoise_step.  Embeddings, adapter projections and
+    the hint copies are left out (generous to the CPU).  Returns (cpu_baseline dict, mean measured seconds per step,
+    extrapolated s per denoise step, number of timed steps)."""
     from oracle import ref_import, restate
     cfg, grid, _ = CONFIGS[cfg_name]
     cores = len(os.sched_getaffinity(0))
@@ -189,16 +191,16 @@ def cpu_reference_sample(cfg_name, steps=1, warmup=0, total_budget=150.0, max_st
     run_block(1)                                  # page in / thread pool
     t_cal = run_block(1)
     rate = _block_flops(cfg, gh * gw) / t_cal     # flop/s of this box on the 1-frame block
-    step_budget = min(max_step_seconds, total_budget / max(1, steps + warmup))
+    step_budget = max_step_seconds
     frames = 1
     for f in range(grid[0], 0, -1):
         if _block_flops(cfg, f * gh * gw) / rate <= step_budget:
             frames = f
             break
     Ls, sgrid = frames * gh * gw, (frames, gh, gw)
-    for _ in range(warmup):
-        run_block(frames)
-    times = [run_block(frames) for _ in range(steps)]
+    est = _block_flops(cfg, Ls) / rate
+    n_timed = max(1, min(int(steps), int(total_budget / max(est, 1e-3))))
+    times = [run_block(frames) for _ in range(n_timed)]
     t_step = sum(times) / len(times)
     n_blocks = cfg["num_layers"] + len(range(0, cfg["num_layers"], 2))
     B = 2
@@ -209,22 +211,24 @@ def cpu_reference_sample(cfg_name, steps=1, warmup=0, total_budget=150.0, max_st
     cb = dict(value=tokens_per_s, unit="tokens/s", cores=cores, kind=kind,
               sample=f"{what} fp32 on {cores} threads; one step = 1 block of {n_blocks} at dim {D} on 1 sample of the CFG "
                      f"pair, {Ls} tokens = {sgrid} of the {grid[0]}x{gh}x{gw} grid (frames from a 1-frame calibration for "
-                     f"~{step_budget:.1f} s/step); {warmup} warm-up + {len(times)} timed step(s), {t_step:.2f} s/step, "
+                     f"<= {step_budget:.0f} s/step, independent of --steps); {len(times)} timed step(s), {t_step:.2f} s/step, "
                      f"{_block_flops(cfg, Ls) / t_step / 1e12:.2f} TFLOP/s; full-grid block = x{scale_up:.2f} by flop count; "
                      f"denoise step = x{n_blocks} blocks x{B} CFG = {s_denoise:.0f} s; tokens/s = {B}*{L_full}/that")
-    return cb, t_step, s_denoise
+    return cb, t_step, s_denoise, len(times)
 
 
 def run_reference_arm(args):
-    """`bench.py --impl reference`: exactly --warmup + --steps bounded-sample steps on the host cores; `ms_per_step` is the
-    measured time of one such step (so steps x ms_per_step is this run's wall clock), `value` the metric extrapolated
+    """`bench.py --impl reference`: full-grid blocks on the host cores (the bounded sample of cpu_reference_sample — the same
+    one whatever --steps / --warmup say); `steps` in the line = blocks actually timed (<= --steps, capped by the time budget),
+    `ms_per_step` the measured time of one (so steps x ms_per_step is the timed wall clock), `value` the metric extrapolated
     from it as cpu_baseline.sample states."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cb, t_step, s_denoise = cpu_reference_sample(args.config, steps=max(1, args.steps), warmup=max(0, args.warmup))
+    cb, t_step, s_denoise, n_timed = cpu_reference_sample(args.config, steps=max(1, args.steps))
     line = {"impl": "reference", "metric": "video_tokens_per_s", "value": cb["value"], "unit": "tokens/s",
-            "n_gpus": args.gpus, "steps": max(1, args.steps), "warmup": max(0, args.warmup), "ms_per_step": t_step * 1e3,
+            "n_gpus": args.gpus, "steps": n_timed, "warmup": 0, "requested": {"steps": args.steps, "warmup": args.warmup},
+            "ms_per_step": t_step * 1e3,
             "s_per_denoise_step": s_denoise, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": bench_config(args.config, int(os.environ.get("WORLD_SIZE", "1"))),
             "reference_run": "host CPU; ms_per_step = one bounded-sample step (see cpu_baseline.sample), "
@@ -435,10 +439,21 @@ def run_gpu_arm(args):
     if sp_parity is not None:
         line["sp_parity"] = sp_parity
         line["per_rank_ms_per_step"] = per_rank
+    if world == 1 and not args.no_gpu_reference:
+        # the bar on the same box (BASELINE.md §4 B-GPU-ref): one block of the reference's own module (autocast bf16 +
+        # flash-attn) next to the same block on this repo's kernels, at this config's shape — after every timed region
+        try:
+            model.release_workspace()
+            torch.cuda.empty_cache()
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            from ref_gpu_block import measure_block
+            line["gpu_reference"] = measure_block(model, cfg, (grid[0], grid[1] // 2, grid[2] // 2), iters=3, B=B)
+        except Exception as e:  # noqa: BLE001
+            line["gpu_reference"] = {"unavailable": repr(e)[:300]}
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             try:
-                line["cpu_baseline"] = cpu_reference_sample(args.config, steps=1, warmup=0)[0]
+                line["cpu_baseline"] = cpu_reference_sample(args.config, steps=2)[0]
             except Exception as e:  # noqa: BLE001
                 line["cpu_baseline"] = {"error": repr(e)[:200]}
         print(json.dumps(line), flush=True)
@@ -456,6 +471,7 @@ def main():
     ap.add_argument("--config", default=os.environ.get("VC_BENCH_CONFIG", "c3"), choices=sorted(CONFIGS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-reference", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

@@ -7,14 +7,16 @@ import torch
 from . import restate
 
 
-def run_reference(ref_mods, cfg, grid, seed, scale=1.0, t_value=500.0, device="cuda", dtype=torch.bfloat16):
-    """-> dict with the reference's bf16 output and, per block, the tensors its forward saw / returned."""
+def run_reference(ref_mods, cfg, grid, seed, scale=1.0, t_value=500.0, device="cuda", dtype=torch.bfloat16, seq_pad=0):
+    """-> dict with the reference's bf16 output and, per block, the tensors its forward saw / returned.  seq_pad > 0 asks
+    for seq_len = L + seq_pad: the reference zero-pads the token rows and masks them as keys (k_lens = L < seq_len)."""
     base, vc = ref_mods
     sd = restate.synth_state_dict(cfg, seed=seed, device=device, dtype=dtype)
     ref = vc.VerseCrafterWanTransformer3DModel(**cfg)
     ref.load_state_dict(sd, strict=True)
     ref = ref.to(device=device, dtype=dtype).eval().requires_grad_(False)
     inp = restate.synth_inputs(cfg, grid, seed=seed, device=device, t_value=t_value)
+    inp["seq_len"] += int(seq_pad)
     cap = {}
 
     def backbone_hook(i):

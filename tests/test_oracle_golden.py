@@ -92,3 +92,25 @@ def test_forward_matches_live_reference_when_present():
     y = restate.forward(sd, cfg, inp["x"], inp["t"], inp["geoada_context"], inp["context"], inp["seq_len"],
                         geoada_context_scale=0.5)
     assert relerr(y, y_ref) < 2e-5
+
+
+def test_reference_key_mask_for_padded_sequences_cpu():
+    """The attention() stand-in honours k_lens (wan_transformer3d.py:394-399): with seq_len > L the reference's own model gives
+    the same latents as without padding (fp32, CPU), which un-masked attention over the zero-padded rows would not."""
+    from oracle import ref_import
+    from oracle.ref_run import run_reference
+    if not ref_import.reference_available():
+        pytest.skip("reference sources absent")
+    mods = ref_import.load_reference_modules()
+    cfg = dict(dim=128, ffn_dim=256, num_heads=1, num_layers=3, text_dim=32, geoada_in_dim=128, geoada_layers=[0, 1])
+    a = run_reference(mods, cfg, (2, 6, 10), 5, 0.6, device="cpu", dtype=torch.float32)
+    b = run_reference(mods, cfg, (2, 6, 10), 5, 0.6, device="cpu", dtype=torch.float32, seq_pad=9)
+    assert b["cap"]["blk_in.0"].shape[1] == a["cap"]["blk_in.0"].shape[1] + 9
+    assert torch.allclose(a["y"], b["y"], atol=2e-5, rtol=1e-4)
+    from videox_fun.models import attention_utils
+    q = torch.randn(2, 5, 1, 8)
+    k, v = torch.randn(2, 7, 1, 8), torch.randn(2, 7, 1, 8)
+    full = attention_utils.attention(q, k, v, k_lens=torch.tensor([7, 7]))
+    cut = attention_utils.attention(q, k, v, k_lens=torch.tensor([7, 4]))
+    assert torch.equal(full[0], cut[0]) and not torch.allclose(full[1], cut[1])
+    assert torch.allclose(cut[1:], attention_utils.attention(q[1:], k[1:, :4], v[1:, :4]), atol=1e-6)

@@ -41,3 +41,18 @@ def test_c3_full_depth_bf16():
     _save("parity_c3_test.json", res)
     assert res["final_vs_bf16_oracle"]["cosine"] >= 0.999, res
     assert res["teacher_forced_max"] <= 1e-2, res
+
+
+def test_c4_full_depth_bf16():
+    """BASELINE.json config 4 (720p: 81x720x1280, L = 75,600 tokens, Wan2.1-14B + GeoAdapter) on ONE GPU against the bf16
+    oracle with flash-attn — oracle parity for the long grid itself, where the multi-GPU bench lines only compare the
+    sequence-parallel forward with the P=1 forward of this repo.  About a minute; needs the 180 GB part."""
+    if torch.cuda.get_device_properties(0).total_memory < 160 * 2 ** 30:
+        pytest.skip("needs a 180 GB B200")
+    if os.environ.get("VC_SKIP_C4_PARITY") == "1":
+        pytest.skip("VC_SKIP_C4_PARITY=1")
+    from tools import parity_full
+    res = parity_full.run("c4", fp32=False)
+    _save("parity_c4_test.json", res)
+    assert res["final_vs_bf16_oracle"]["cosine"] >= 0.999, res
+    assert res["teacher_forced_max"] <= 1e-2, res

@@ -103,3 +103,55 @@ def test_reference_pipeline_with_the_repo_unipc_scheduler_gpu():
         assert cosine(outs[0], outs[1]) >= 0.999, cosine(outs[0], outs[1])
     finally:
         mod.FlowUniPCMultistepScheduler = saved
+
+
+# ---- TeaCache / cfg-skip: the CLI's default production path (inference/versecrafter_inference.py:104-118, :306-313) ----------
+from tests.golden import gen_golden_teacache as GT  # noqa: E402
+
+GOLD_TC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pipeline_teacache.npz")
+
+
+@needs_ref
+@pytest.mark.parametrize("case", sorted(GT.CASES))
+def test_reference_teacache_loop_cpu_matches_golden(case):
+    """CPU: the reference's own skip logic (wan_transformer3d.py:205-245) and forward branches
+    (wan_transformer3d_versecrafter.py:384-417, :438-441) inside its own pipeline reproduce the committed fixture: decisions,
+    counter (reset when cnt reaches num_steps) and latents.  The fixture really skips (3 of 8 steps) and really differs from
+    the run without TeaCache."""
+    g = np.load(GOLD_TC)
+    ref, _ = G.reference_model()
+    lat, calc, cnt = GT.run_case(ref, "cpu", torch.float32, **GT.CASES[case])
+    assert calc == g[f"{case}.calc"].tolist() == [1, 1, 0, 1, 0, 1, 0, 1]
+    assert cnt == g[f"{case}.cnt"].tolist() == [1, 2, 3, 4, 5, 6, 7, 0]
+    gold = torch.from_numpy(g[f"{case}.latents"])
+    assert relerr(lat, gold) < 1e-5
+    assert relerr(torch.from_numpy(g["plain.latents"]), gold) > 1e-4
+    assert ref.teacache is None and ref.cfg_skip_ratio is None      # run_case leaves the model as it found it
+
+
+@needs_ref
+@pytest.mark.gpu
+@pytest.mark.parametrize("case,offload", [("teacache", False), ("teacache", True), ("teacache_cfgskip", True)])
+def test_dropin_teacache_loop_matches_the_reference_gpu(case, offload):
+    """GPU: the same unmodified loop, TeaCache on, around the drop-in: the SAME should_calc sequence and counter as the
+    reference's code (fixture and the reference's own bf16 run on this GPU), latents within north_star's tolerance of both;
+    `offload=True` (residual parked on the host, the reference's default) changes nothing; under cfg-skip the late steps run the
+    text-conditioned half and reuse the matching slice of the cached residual."""
+    from versecrafter_b200.transformer import VerseCrafterWanTransformer3DModel
+    g = np.load(GOLD_TC)
+    ref16, sd = G.reference_model("cuda", torch.bfloat16)
+    model = VerseCrafterWanTransformer3DModel(**G.CFG, device="cuda", dtype=torch.bfloat16, init=False)
+    model.load_state_dict(sd, strict=True)
+    model.eval()
+    kw = GT.CASES[case]
+    lat, calc, cnt = GT.run_case(model, "cuda", torch.bfloat16, offload=offload, **kw)
+    lat_ref, calc_ref, cnt_ref = GT.run_case(ref16, "cuda", torch.bfloat16, offload=offload, **kw)
+    assert calc == calc_ref == g[f"{case}.calc"].tolist()
+    assert cnt == cnt_ref == g[f"{case}.cnt"].tolist()          # ends at 0: reset when cnt == num_steps
+    gold = torch.from_numpy(g[f"{case}.latents"]).cuda()
+    assert torch.isfinite(lat.float()).all()
+    assert cosine(lat, gold) >= 0.999, cosine(lat, gold)
+    assert cosine(lat, lat_ref) >= 0.999, cosine(lat, lat_ref)
+    if offload:                                                    # where the residual lives is not arithmetic
+        lat_dev, _, _ = GT.run_case(model, "cuda", torch.bfloat16, offload=False, **kw)
+        assert torch.equal(lat, lat_dev)

@@ -154,6 +154,52 @@ def test_dropin_matches_the_reference_under_autocast(ref_mods, name):
               final_cosine=cosine(y, r["y"]), final_rel_l2=relerr(y, r["y"]), worst_teacher_forced_block_rel_l2=worst))
 
 
+@pytest.mark.parametrize("name,pad", [("tiny4", 40), ("geo013", 7)])
+def test_padded_sequence_key_mask_matches_the_reference(ref_mods, name, pad):
+    """seq_len > L: the reference zero-pads the embedded rows to seq_len and passes k_lens = L to attention()
+    (wan_transformer3d.py:181-202, :394-399), so the padded rows are computed as queries but never attended as keys.  The
+    drop-in's key masking (k_len in the attention kernel; l_true under sequence parallelism, which tools/sp_check.py ties
+    bit for bit to this P=1 path) is compared here with the reference's own modules — final latents within north_star's
+    tolerance, and both must differ from what un-masked attention over the padded rows would give."""
+    from versecrafter_b200.transformer import VerseCrafterWanTransformer3DModel
+    cfg, grid, seed, scale = CASES[name]
+    r = run_reference(ref_mods, cfg, grid, seed, scale, seq_pad=pad)
+    r0 = run_reference(ref_mods, cfg, grid, seed, scale)
+    inp = r["inp"]
+    assert r["cap"]["blk_in.0"].shape[1] == inp["seq_len"] == r0["inp"]["seq_len"] + pad
+    model = VerseCrafterWanTransformer3DModel(**cfg, device="cuda", dtype=torch.bfloat16, init=False)
+    model.load_state_dict(r["sd"], strict=True)
+    model.eval()
+    y = model(x=inp["x"].bfloat16(), t=inp["t"], geoada_context=inp["geoada_context"].bfloat16(), context=inp["context"],
+              seq_len=inp["seq_len"], geoada_context_scale=scale)
+    assert cosine(y, r["y"]) >= 0.999, cosine(y, r["y"])
+    assert relerr(y, r["y"]) < 3e-2
+    # masking means padding changes nothing but rounding: the reference with and without padding agree
+    assert cosine(r["y"], r0["y"]) >= 0.9995
+    _log(dict(test="dropin_vs_reference_padded_keys", case=name, pad=pad, final_cosine=cosine(y, r["y"]),
+              final_rel_l2=relerr(y, r["y"]), reference_padded_vs_unpadded_cosine=cosine(r["y"], r0["y"])))
+
+
+def test_c2_full_size_dropin_matches_the_reference_model(ref_mods):
+    """Full size, the reference ITSELF (not its restatement): the reference's VerseCrafterWanTransformer3DModel at c2
+    (1.3B architecture, 30 + 15 blocks, dim 1536, 12 heads, L = 32,760, CFG batch 2) under autocast(bf16) + flash_attn against
+    the drop-in on the same weights and inputs (tools/ref_gpu_full.py) — the shapes where tile tails, K = 8,960 and 30-block
+    drift matter.  north_star's tolerance: final cosine >= 0.999, teacher-forced blocks <= 1e-2.  Both forwards are timed
+    (CUDA events) and the record goes to gpurun_out/ref_gpu_full_c2_test.json."""
+    import json
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import ref_gpu_full
+    rec = ref_gpu_full.run("c2", iters=2, log=lambda *a: None)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "ref_gpu_full_c2_test.json"), "w") as f:
+        f.write(json.dumps(rec) + "\n")
+    assert rec["reference_attention"] == "flash_attn"
+    assert rec["final_cosine"] >= 0.999, rec
+    assert rec["worst_teacher_forced"] <= 1e-2, rec["teacher_forced_rel_l2"]
+    assert len(rec["teacher_forced_rel_l2"]) == 5
+
+
 def test_reference_copy_is_unmodified():
     """What the tests above import is the reference, byte for byte (digests pinned in oracle/ref_manifest.json)."""
     from oracle import build_ref

@@ -138,3 +138,37 @@ def test_interleaved_schedule_order(monkeypatch, num_layers, geo_layers):
         assert covered == 4 * n_geo - 3   # layer 0 (hint 0 is due there); block 0's first slot starts with before_proj
     else:
         assert covered >= n_geo
+
+
+def _bare_exchange():
+    """A PeerExchange without a process group: only the time-out bookkeeping (the fields check_status touches)."""
+    from versecrafter_b200 import sp
+    px = object.__new__(sp.PeerExchange)
+    px.poisoned, px.timeout_ms, px.first_timeout_ms, px.first_epochs = None, 5000, 60000, 512
+    px.barrier_impl, px._flags, px._epoch = "own", None, 0
+    px._status, px._status_host, px._status_event = None, None, None
+    return px
+
+
+def test_barrier_timeout_poisons_the_exchange():
+    """A barrier that timed out must not be survivable: the status word on the GPU is sticky (later waits return at once), so
+    after the first report every barrier / signal / wait / check raises instead of running unsynchronised."""
+    from versecrafter_b200 import _lib
+    px = _bare_exchange()
+    px._check_alive()                                            # healthy: no exception
+    px._status_host = torch.tensor([0], dtype=torch.int32)
+    px._raise_if_timed_out()                                     # status 0: nothing
+    px._status_host = torch.tensor([-(1 << 31) | 3], dtype=torch.int32)   # 0x80000003: rank 3 never arrived
+    with pytest.raises(_lib.VCError, match="rank 3"):
+        px._raise_if_timed_out()
+    assert px.poisoned is not None
+    for call in (px.barrier, px.signal, lambda: px.wait(7), px._check_alive):
+        with pytest.raises(_lib.VCError, match="unusable"):
+            call()
+
+
+def test_barrier_timeout_is_longer_for_the_first_epochs(monkeypatch):
+    px = _bare_exchange()
+    assert px._timeout(1) == 60000 and px._timeout(512) == 60000 and px._timeout(513) == 5000
+    px.timeout_ms, px.first_timeout_ms = 90000, 90000            # VC_SP_BARRIER_TIMEOUT_MS above the first-epoch default
+    assert px._timeout(1) == 90000 and px._timeout(10 ** 6) == 90000

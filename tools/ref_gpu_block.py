@@ -48,14 +48,11 @@ def timed(fn, iters):
 
 
 @torch.no_grad()
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--iters", type=int, default=3)
-    args = ap.parse_args()
-    cfg = dict(dim=5120, ffn_dim=13824, num_heads=40, num_layers=1, text_dim=4096, geoada_in_dim=128)
-    grid = (21, 30, 52)
-    L, B, D = grid[0] * grid[1] * grid[2], 2, cfg["dim"]
-    model = VerseCrafterWanTransformer3DModel(**cfg, device="cuda", dtype=torch.bfloat16, init=False).synthetic_init_(0)
+def measure_block(model, cfg, grid, iters=3, B=2):
+    """One DiT block (model.blocks[0]) at `grid` (latent F, H', W' AFTER patching), CFG batch B: the reference's module
+    under autocast(bf16) + flash_attn vs the drop-in's kernels, same weights, same inputs.  Used by main() below and by
+    bench.py's `gpu_reference` object (outside its timed region)."""
+    L, D = grid[0] * grid[1] * grid[2], cfg["dim"]
     blk = model.blocks[0]
     g = torch.Generator(device="cuda").manual_seed(1)
     x = torch.randn(B, L, D, generator=g, device="cuda").bfloat16()
@@ -70,18 +67,34 @@ def main():
     assert attention_utils.LAST_IMPL == "flash_attn", attention_utils.LAST_IMPL
     y = model.block_forward("blocks", 0, x, e0, ctx, grid)
     rel = float((y.float() - y_ref.float()).norm() / y_ref.float().norm())
-    ref_ms, ref_min = timed(lambda: reference_block_forward(ref, x, e0, ctx, grid, freqs), args.iters)
+    del y, y_ref
+    ref_ms, ref_min = timed(lambda: reference_block_forward(ref, x, e0, ctx, grid, freqs), iters)
     st = SimpleNamespace(B=B, Lp=L, grid=grid, rope=model._rope(grid), k_len=L, l_true=L, step_cache=None)
     x2d = x.reshape(B * L, D).clone()
     c2d = ctx.reshape(-1, D).contiguous()
-    ours_ms, ours_min = timed(lambda: model._block(blk, x2d, m, c2d, st), args.iters * 2)
+    ours_ms, ours_min = timed(lambda: model._block(blk, x2d, m, c2d, st), iters * 2)
     flop = B * (12 * L * D * D + 4 * 512 * D * D + 4 * L * D * cfg["ffn_dim"] + 4 * L * L * D + 4 * L * 512 * D)
-    rec = dict(what="one DiT block at the c3 shape: reference module (eager PyTorch + cuBLASLt + flash-attn) vs this repo, same weights and inputs, 1xB200", shape=[B, L, D], block_tflop=flop / 1e12,
-               eager_pytorch_fa2_ms=ref_ms, eager_pytorch_fa2_ms_min=ref_min, eager_tflops=flop / ref_ms / 1e9,
-               this_repo_ms=ours_ms, this_repo_ms_min=ours_min, this_repo_tflops=flop / ours_ms / 1e9,
-               speedup=ref_ms / ours_ms, rel_l2_between_them=rel, step_extrapolation_s=dict(eager=ref_ms * 60 / 1e3, ours=ours_ms * 60 / 1e3),
-               reference_source=ref_import.REF_ROOT, reference_attention=attention_utils.LAST_IMPL,
-               note="reference side = the reference's own WanAttentionBlock module under autocast(bf16); excludes its hint stack/unbind copies (~150 GB/step)")
+    n_blocks = cfg["num_layers"] + len(range(0, cfg["num_layers"], 2))
+    rec = dict(what="one DiT block: the reference's own WanAttentionBlock (eager PyTorch + cuBLASLt + flash-attn, autocast bf16) "
+                    "vs this repo's kernels, same weights and inputs, same GPU",
+               shape=[B, L, D], block_tflop=flop / 1e12, block_ms_ref=ref_ms, block_ms_ref_min=ref_min,
+               ref_tflops=flop / ref_ms / 1e9, block_ms_repo=ours_ms, block_ms_repo_min=ours_min,
+               repo_tflops=flop / ours_ms / 1e9, speedup=ref_ms / ours_ms, rel_l2_between_them=rel,
+               reference_source=os.path.relpath(ref_import.REF_ROOT), reference_attention=attention_utils.LAST_IMPL,
+               note="reference side excludes its hint stack / unbind copies and per-step embeddings (generous to it)")
+    del ref, x, x2d, ctx, c2d
+    torch.cuda.empty_cache()
+    return rec
+
+
+@torch.no_grad()
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--iters", type=int, default=3)
+    args = ap.parse_args()
+    cfg = dict(dim=5120, ffn_dim=13824, num_heads=40, num_layers=1, text_dim=4096, geoada_in_dim=128)
+    model = VerseCrafterWanTransformer3DModel(**cfg, device="cuda", dtype=torch.bfloat16, init=False).synthetic_init_(0)
+    rec = measure_block(model, cfg, (21, 30, 52), args.iters)
     print(json.dumps(rec), flush=True)
     os.makedirs("gpurun_out", exist_ok=True)
     with open("gpurun_out/ref_gpu_block.json", "w") as f:

@@ -34,15 +34,23 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+std::mutex& setup_mutex() {
+  static std::mutex m;
+  return m;
+}
+
+// One host thread per GPU is a supported way to drive the library, so the per-device caches are atomics: two threads that
+// miss at the same time both query the driver and store the same value.
 int sm_count() {
-  static int n[kMaxDevices] = {};
+  static std::atomic<int> n[kMaxDevices];
   const int dev = current_device();
-  if (n[dev] == 0) {
-    int v = 0;
+  int v = n[dev].load(std::memory_order_relaxed);
+  if (v == 0) {
     cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
-    n[dev] = v > 0 ? v : 148;
+    if (v <= 0) v = 148;
+    n[dev].store(v, std::memory_order_relaxed);
   }
-  return n[dev];
+  return v;
 }
 
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,

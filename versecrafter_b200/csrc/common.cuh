@@ -6,6 +6,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+#include <mutex>
+
 namespace vc {
 
 // ---------------------------------------------------------------------------------------------------
@@ -313,6 +316,7 @@ __device__ __forceinline__ void reg_alloc() {
 // ---------------------------------------------------------------------------------------------------
 namespace vc_host {
 void set_error(const char* fmt, ...);
+std::mutex& setup_mutex();  // guards the once-per-device set-up paths (kernel attributes); never held across a launch
 // 2-D .. 4-D bf16 tensor map, 128-byte swizzle, zero OOB fill. dims/strides innermost first; strides in BYTES
 // for dims 1.. (dim 0 is contiguous).  Returns 0 on success.
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
@@ -340,15 +344,19 @@ int sm_count();  // multiprocessors of the current device (cached per device)
 // may grow between calls).  Wrap a template-id kernel in parentheses.
 #define VC_ENSURE_DYN_SMEM(kernel, bytes, what)                                                                      \
   do {                                                                                                               \
-    static int done__[vc_host::kMaxDevices] = {};                                                                    \
+    static std::atomic<int> done__[vc_host::kMaxDevices]; /* static storage: starts at 0 */                          \
     const int dev__ = vc_host::current_device();                                                                     \
-    if (done__[dev__] < (int)(bytes)) {                                                                              \
-      cudaError_t e__ = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes));     \
-      if (e__ != cudaSuccess) {                                                                                      \
-        vc_host::set_error("%s: cannot set %d B dynamic smem: %s", what, (int)(bytes), cudaGetErrorString(e__));     \
-        return (int)e__;                                                                                             \
+    if (done__[dev__].load(std::memory_order_acquire) < (int)(bytes)) {                                              \
+      /* slow path, once per (kernel, device, size): host threads driving different GPUs serialise here */          \
+      std::lock_guard<std::mutex> lock__(vc_host::setup_mutex());                                                    \
+      if (done__[dev__].load(std::memory_order_relaxed) < (int)(bytes)) {                                            \
+        cudaError_t e__ = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes));   \
+        if (e__ != cudaSuccess) {                                                                                    \
+          vc_host::set_error("%s: cannot set %d B dynamic smem: %s", what, (int)(bytes), cudaGetErrorString(e__));   \
+          return (int)e__;                                                                                           \
+        }                                                                                                            \
+        done__[dev__].store((int)(bytes), std::memory_order_release);                                                \
       }                                                                                                              \
-      done__[dev__] = (int)(bytes);                                                                                  \
     }                                                                                                                \
   } while (0)
 

@@ -101,6 +101,10 @@ class VerseCrafterWan22ExpertSwitch(nn.Module):
             for m in self._both():
                 m.current_steps = v
 
+    def check_sp_status(self):
+        """Blocking sequence-parallel barrier check after a denoise loop (the experts share one exchange)."""
+        self.low_noise_model.check_sp_status()
+
     def enable_teacache(self, *a, **kw):
         for m in self._both():
             m.enable_teacache(*a, **kw)

@@ -120,4 +120,6 @@ def denoise(transformer, latents, geoada_ctx, context, sigmas=None, guidance_sca
             x = scheduler.step_cfg(pred[0:1], pred[1:2] if do_cfg else None, x, guidance_scale)
         if callback is not None:
             callback(i, t, x)
+    if hasattr(transformer, "check_sp_status"):
+        transformer.check_sp_status()   # sequence parallelism: no barrier of the loop timed out (blocking, once per loop)
     return x

@@ -81,6 +81,22 @@ class PeerExchange:
         self.barrier_impl = os.environ.get("VC_SP_BARRIER", "own")         # own | torch
         self._flags, self._status, self._epoch = None, None, 0
         self._status_host, self._status_event = None, None
+        # barrier time-out: VC_SP_BARRIER_TIMEOUT_MS for steady state; the first epochs of a process get at least
+        # VC_SP_BARRIER_FIRST_TIMEOUT_MS because ranks reach their first forward seconds apart (module loading, first
+        # rendezvous, a profiler or debugger attached to one rank)
+        self.timeout_ms = int(os.environ.get("VC_SP_BARRIER_TIMEOUT_MS", "5000"))
+        self.first_timeout_ms = max(self.timeout_ms, int(os.environ.get("VC_SP_BARRIER_FIRST_TIMEOUT_MS", "60000")))
+        self.first_epochs = 512    # more than the barriers of one c3 forward (4 per block x 60 + GeoAdapter)
+        self.poisoned = None       # message of the time-out that killed this group; every later call raises it
+
+    def _timeout(self, epoch):
+        return self.first_timeout_ms if epoch <= self.first_epochs else self.timeout_ms
+
+    def _check_alive(self):
+        from . import _lib
+        if self.poisoned is not None:
+            raise _lib.VCError(f"sequence-parallel group unusable: {self.poisoned} (the ranks are no longer in step; "
+                               f"tear the process group down and start again)")
 
     def side_stream(self):
         """High-priority stream for the q / k scatter launches that run under the next GEMM (ulysses_qkv_attention_overlapped)."""
@@ -117,10 +133,11 @@ class PeerExchange:
             if self.barrier_impl == "torch":
                 next(iter(self.bufs.values()))[2].barrier(channel=0)
                 return
+            self._check_alive()
             self._ensure_flags()
             self._epoch += 1
             lib = _lib.load()
-            _lib.check(lib.vc_peer_barrier(self._flags, self.rank, self.P, self._epoch & 0xFFFFFFFF, 0,
+            _lib.check(lib.vc_peer_barrier(self._flags, self.rank, self.P, self._epoch & 0xFFFFFFFF, self._timeout(self._epoch),
                                            ops._ptr(self._status), ops._stream()), "vc_peer_barrier")
             ops.launch_count += 1
 
@@ -132,6 +149,7 @@ class PeerExchange:
         from . import _lib, ops
         if self.barrier_impl == "torch":
             return None
+        self._check_alive()
         self._ensure_flags()
         self._epoch += 1
         with ops._timed("barrier", 0.0):
@@ -145,36 +163,41 @@ class PeerExchange:
         from . import _lib, ops
         if epoch is None:
             return self.barrier()
+        self._check_alive()
         with ops._timed("barrier", 0.0):
-            _lib.check(_lib.load().vc_peer_wait(self._flags, self.rank, self.P, epoch & 0xFFFFFFFF, 0, ops._ptr(self._status),
-                                                ops._stream()), "vc_peer_wait")
+            _lib.check(_lib.load().vc_peer_wait(self._flags, self.rank, self.P, epoch & 0xFFFFFFFF, self._timeout(epoch),
+                                                ops._ptr(self._status), ops._stream()), "vc_peer_wait")
             ops.launch_count += 1
 
     def check_status(self, wait=False):
-        """Raises if a barrier of an EARLIER forward timed out (a peer never arrived).  Non-blocking by default: every call
-        queues an asynchronous copy of the status word to pinned host memory and looks at the copy queued by the previous
-        call once its event has completed, so the caller's launch queue is never drained; wait=True synchronises."""
-        from . import _lib
+        """Raises if a barrier timed out (a peer never arrived).  wait=False: every call queues an asynchronous copy of the
+        status word to pinned host memory and looks at the copy queued by the PREVIOUS call once its event has completed,
+        so the launch queue is never drained — but a time-out inside the forward that has just been enqueued is only seen
+        by the next call.  wait=True: copies the word after everything enqueued so far and synchronises on it, so it
+        covers the current forward; the drop-in does this on the last step of a denoise loop (transformer.forward) and
+        loop.denoise after its last step.  The status word on the GPU is sticky (every later wait returns at once, see
+        csrc/peer_sync.cu), so a time-out poisons the group: this and every later barrier / signal / wait raise."""
         if self._status is None:
             return
+        self._check_alive()
         if self._status_host is None:
             self._status_host = torch.zeros(1, dtype=torch.int32).pin_memory()
             self._status_event = torch.cuda.Event()
-        elif wait or self._status_event.query():
-            if wait:
-                self._status_event.synchronize()
-            v = int(self._status_host[0])
-            if v != 0:
-                raise _lib.VCError(f"sequence-parallel barrier timed out waiting for rank {v & 0xff} (status {v & 0xffffffff:#x})")
-        else:
+        elif self._status_event.query():
+            self._raise_if_timed_out()
+        elif not wait:
             return   # the previous copy is still in flight: look again next time
         self._status_host.copy_(self._status, non_blocking=True)
         self._status_event.record()
         if wait:
             self._status_event.synchronize()
-            v = int(self._status_host[0])
-            if v != 0:
-                raise _lib.VCError(f"sequence-parallel barrier timed out waiting for rank {v & 0xff} (status {v & 0xffffffff:#x})")
+            self._raise_if_timed_out()
+
+    def _raise_if_timed_out(self):
+        v = int(self._status_host[0])
+        if v != 0:
+            self.poisoned = f"barrier timed out waiting for rank {v & 0xff} (status {v & 0xffffffff:#x})"
+            self._check_alive()
 
 
 def recv_layout_index(which, b, t, h, n_batch, l_total, heads_per_peer, head_dim):

@@ -387,6 +387,12 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
                         print(f"[versecrafter_b200] symmetric memory unavailable ({e!r}); using NCCL all_to_all", flush=True)
         return self._px
 
+    def check_sp_status(self):
+        """Blocking check that no cross-GPU barrier of the forwards enqueued so far timed out (raises VCError and poisons
+        the exchange if one did).  Call it once after a denoise loop, before the result is used; no-op without SP."""
+        if self.sp_world_size > 1 and self._peer_exchange() is not None:
+            self._peer_exchange().check_status(wait=True)
+
     def all_gather(self, x, dim=1):
         return sp.all_gather_tokens(x, dim, self.sp_group)
 
@@ -899,7 +905,12 @@ class VerseCrafterWanTransformer3DModel(nn.Module):
         if P > 1:
             yv = self.all_gather(yv, dim=1)
             if self._peer_exchange() is not None:
-                self._peer_exchange().check_status()   # a timed-out cross-GPU barrier raises here instead of returning garbage
+                # a cross-GPU barrier that timed out leaves unsynchronised garbage in this forward.  The non-blocking check
+                # sees the PREVIOUS forward's status (no queue drain per step); the last step of a denoise loop
+                # (current_steps / num_inference_steps are set by the pipeline, :869,:872) checks its own forward with a
+                # synchronisation, so the latents that go to the VAE are never from a timed-out step.
+                last = self.num_inference_steps is not None and self.current_steps >= self.num_inference_steps - 1
+                self._peer_exchange().check_status(wait=last)
         out = torch.stack([ops.unpatchify(yv[b], grid, self.out_dim) for b in range(B)])
         if self.teacache is not None and cond_flag:
             self.teacache.cnt += 1
