@@ -183,9 +183,19 @@ def test_render_control_maps_chain_matches_oracle_chain():
         want = cr.masked_projection(g_rgb, g_alpha)
         diff = (out["3D_gaussian_RGB"][f].cpu().int() - want.int()).abs()
         assert int(diff.max()) <= 1 and float((diff > 0).float().mean()) < 0.02
+        # step 10 preview (:1350-1373): exact composition of the kernel's own blend / alpha, and the all-oracle chain within the
+        # projection's one-count tolerance (pixels whose alpha sits on the 0.001 visibility edge may flip: < 2 %)
+        kb, ka = out["gaussian_blend"][f].cpu(), out["gaussian_alpha"][f].cpu()
+        want10, _ = cr.composite_by_depth(t(bg_rgb), t(bg_depth), kb, t(fg_depth), ka > 0.001)
+        assert torch.equal(out["background_and_3D_gaussian"][f].cpu(), want10)
+        full10, _ = cr.composite_by_depth(t(bg_rgb), t(bg_depth), cr.blend_with_bg(g_rgb, g_alpha, t(bg_rgb)), t(fg_depth), g_alpha > 0.001)
+        d10 = (out["background_and_3D_gaussian"][f].cpu().int() - full10.int()).abs()
+        assert float((d10 > 1).float().mean()) < 0.02
+        assert not torch.equal(want10, t(bg_rgb))           # the Gaussians are really in the picture
     # the range is the quantile pair of all positive depths of the three stacks
     _, comb = cm.composite_by_depth(out["background_RGB"], out["bg_depth"], torch.zeros_like(out["background_RGB"]), out["fg_depth"], out["fg_mask"])
     assert (lo, hi) == cm.compute_global_depth_range([out["bg_depth"], out["fg_depth"], comb])
     # no Gaussians at all -> black projection video, everything else unchanged
     out0 = cm.render_control_maps(torch.from_numpy(pts).cuda(), torch.from_numpy(col).cuda(), [[]] * N, [], idx, [K] * N, Ts, (H, W), point_size=0.06)
     assert int(out0["3D_gaussian_RGB"].max()) == 0 and not bool(out0["fg_mask"].any()) and torch.equal(out0["background_RGB"], out["background_RGB"])
+    assert torch.equal(out0["background_and_3D_gaussian"], out0["background_RGB"])

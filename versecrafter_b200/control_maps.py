@@ -160,8 +160,9 @@ def render_control_maps(background_points, background_colors, ellipsoids_per_fra
                         gaussian_mask_threshold=0.05, depth_range=None, scale_factor=2.0, subdivisions=3):
     """Steps 5-9 of the reference renderer's main() (:1240-1330) on this library's kernels, whole frame stacks at once:
     background point-cloud splat, ellipsoid depth/mask, global-range depth -> gray, merged mask, 3D-Gaussian RGB
-    projection.  Returns the five control videos the VerseCrafter pipeline consumes as uint8 [N, H, W, 3] CUDA tensors
-    (names = the reference's output files) plus the intermediate depths/masks.
+    projection, and step 10's preview composite (:1350-1373, "background_and_3D_gaussian").  Returns the five control videos
+    the VerseCrafter pipeline consumes and the preview as uint8 [N, H, W, 3] CUDA tensors (names = the reference's output
+    files) plus the intermediate depths/masks.
       background_points fp32 [P,3], background_colors uint8 [P,3] (CUDA); ellipsoids_per_frame: per frame a list of
       (mean[3], cov[3,3]) (may be empty); gaussian_params_per_frame: per frame {obj_id: (mean, cov)};
       intrinsics [N,3,3], extrinsics [N,4,4]; image_size = (H, W)."""
@@ -188,9 +189,15 @@ def render_control_maps(background_points, background_colors, ellipsoids_per_fra
     }
     gp = list(gaussian_params_per_frame) + [{}] * (N - len(gaussian_params_per_frame))
     if any(len(p) for p in gp):
-        _, _, _, masked = project_3d_gaussians_to_2d(gp, obj_id_to_color_idx, intrinsics, extrinsics, (W, H),
-                                                     threshold=gaussian_mask_threshold, device=dev, background_frames=bg_rgb)
+        _, alpha, blend, masked = project_3d_gaussians_to_2d(gp, obj_id_to_color_idx, intrinsics, extrinsics, (W, H),
+                                                             threshold=gaussian_mask_threshold, device=dev, background_frames=bg_rgb)
         out["3D_gaussian_RGB"] = masked
+        # step 10 (:1353-1373), the preview video: the Gaussian colours alpha-blended over the background
+        # (blend_gaussian_projection_with_bg, written by the projection kernel), then depth-composited against the background
+        # with the ellipsoid depth, visible where alpha > 0.001 (merge_bg_and_fg_sequences -> composite_by_depth)
+        out["gaussian_alpha"], out["gaussian_blend"] = alpha, blend
+        out["background_and_3D_gaussian"], _ = composite_by_depth(bg_rgb, bg_depth, blend, fg_depth, alpha > 0.001)
     else:
         out["3D_gaussian_RGB"] = torch.zeros_like(bg_rgb)
+        out["background_and_3D_gaussian"] = bg_rgb      # alpha == 0 everywhere: blend == background, nothing visible (:1334-1347)
     return out
